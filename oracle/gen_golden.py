@@ -1,0 +1,348 @@
+"""
+TEST INFRASTRUCTURE ONLY -- generates the golden vectors under tests/golden/ by running the UNMODIFIED
+reference (`/root/reference/Pyrado/pyrado`, imported through `oracle/ref_shim.py`).
+
+Run once in the build container (the GPU box has no /root/reference):
+
+    python oracle/gen_golden.py
+
+Conventions:
+  1. domain parameters are injected as Python floats (fp64),
+  2. actions are float64 arrays in the inner env's units,
+  3. QBB plate angles are read from the reference after reset and stored,
+  4. the cart-pole `_th_ddot` is stored alongside the state,
+  5. files store the state AFTER each step, the reward of each step, `done` and the episode length.
+"""
+import os
+import os.path as osp
+import sys
+import warnings
+
+import numpy as np
+
+HERE = osp.dirname(osp.abspath(__file__))
+sys.path.insert(0, HERE)
+import ref_shim  # noqa: E402
+
+ref_shim.install()
+warnings.filterwarnings("ignore")
+
+import torch  # noqa: E402
+import pyrado  # noqa: E402
+from pyrado.environments.pysim.ball_on_beam import BallOnBeamSim  # noqa: E402
+from pyrado.environments.pysim.one_mass_oscillator import OneMassOscillatorSim  # noqa: E402
+from pyrado.environments.pysim.quanser_ball_balancer import QBallBalancerSim  # noqa: E402
+from pyrado.environments.pysim.quanser_cartpole import QCartPoleSwingUpSim  # noqa: E402
+from pyrado.environments.pysim.quanser_qube import QQubeSwingUpSim  # noqa: E402
+from pyrado.environment_wrappers.action_normalization import ActNormWrapper, ObsActCatWrapper  # noqa: E402
+from pyrado.domain_randomization.default_randomizers import (  # noqa: E402
+    create_default_randomizer_bob,
+    create_default_randomizer_omo,
+    create_default_randomizer_qbb,
+    create_default_randomizer_qcp,
+    create_default_randomizer_qq,
+)
+
+OUT = osp.join(osp.dirname(HERE), "tests", "golden")
+os.makedirs(OUT, exist_ok=True)
+
+
+def make_env(name, **kw):
+    if name == "qq-su":
+        return QQubeSwingUpSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600))
+    if name == "qcp-su":
+        return QCartPoleSwingUpSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600),
+                                   long=kw.get("long", True), simple_dynamics=kw.get("simple_dynamics", False),
+                                   wild_init=kw.get("wild_init", "True"))
+    if name == "qbb":
+        return QBallBalancerSim(dt=kw.get("dt", 0.01), max_steps=kw.get("max_steps", 500),
+                                simple_dynamics=kw.get("simple_dynamics", False))
+    if name == "bob":
+        return BallOnBeamSim(dt=kw.get("dt", 0.01), max_steps=kw.get("max_steps", 500))
+    if name == "omo":
+        return OneMassOscillatorSim(dt=kw.get("dt", 0.02), max_steps=kw.get("max_steps", 300),
+                                    task_args=dict(state_des=np.array([0.5, 0.0])))
+    raise ValueError(name)
+
+
+RANDOMIZERS = {
+    "qq-su": create_default_randomizer_qq,
+    "qcp-su": create_default_randomizer_qcp,
+    "qbb": create_default_randomizer_qbb,
+    "bob": create_default_randomizer_bob,
+    "omo": create_default_randomizer_omo,
+}
+
+
+def param_vector(env):
+    """Domain parameters in the key order of get_nominal_domain_param()."""
+    keys = list(env.get_nominal_domain_param().keys()) if not hasattr(env, "_long") else list(
+        env.get_nominal_domain_param(long=env._long).keys())
+    dp = env.domain_param
+    return keys, np.array([float(dp[k]) for k in keys])
+
+
+def hidden_of(env):
+    if hasattr(env, "_th_ddot") and env._th_ddot is not None:
+        return np.array([float(env._th_ddot)])
+    if hasattr(env, "plate_angs"):
+        return np.array(env.plate_angs, dtype=np.float64).copy()
+    return np.zeros(0)
+
+
+def run_traj(env, init_state, actions, domain_param=None):
+    """Hand loop from Pyrado/tests/test_environments.py:87-91 with injected actions."""
+    if domain_param is not None:
+        domain_param = {k: float(v) for k, v in domain_param.items()}
+    env.reset(init_state=np.asarray(init_state, dtype=np.float64).copy(), domain_param=domain_param)
+    H = actions.shape[0]
+    states = [env.state.copy()]
+    obs = [env.observe(env.state)]
+    hid = [hidden_of(env)]
+    rews, dones = [], []
+    length = H
+    for t in range(H):
+        o, r, d, _ = env.step(actions[t].copy())
+        states.append(env.state.copy())
+        obs.append(np.asarray(o, dtype=np.float64))
+        hid.append(hidden_of(env))
+        rews.append(float(r))
+        dones.append(bool(d))
+        if d:
+            length = t + 1
+            break
+    return dict(states=np.array(states), obs=np.array(obs), hidden=np.array(hid), rews=np.array(rews),
+                dones=np.array(dones), length=length)
+
+
+def gen_env_trajs(name, n_cases=6, H=None, **kw):
+    rng = np.random.RandomState(1234 + sum(map(ord, name)))
+    env = make_env(name, **kw)
+    H = H or env.max_steps
+    cases = {}
+    keys = None
+    for c in range(n_cases):
+        env = make_env(name, **kw)
+        dp = None
+        if c % 2 == 1:
+            # randomized parameters, drawn by the reference's own default randomizer, cast to float (fp64)
+            pyrado.set_seed(100 + c)
+            rz = RANDOMIZERS[name]()
+            rz.randomize(1)
+            dp = {k: float(v) for k, v in rz.get_params(fmt="dict", dtype="numpy").items()}
+        pyrado.set_seed(c)
+        if dp is not None:
+            env.domain_param = dp
+        init = env.init_space.sample_uniform()
+        lo, up = env.act_space.bounds
+        scale = [0.3, 0.3, 1.5, 1.5, 3.0, 0.05][c % 6]  # includes actions beyond the limits and tiny ones (dead zone)
+        actions = rng.uniform(-1, 1, size=(H, lo.size)) * up * scale
+        # piecewise-constant segments make the systems move far enough to hit the state bounds
+        if c >= 2:
+            seg = rng.uniform(-1, 1, size=(H // 25 + 1, lo.size)) * up * scale
+            actions = 0.3 * actions + np.repeat(seg, 25, axis=0)[:H]
+        tr = run_traj(env, init, actions, dp)
+        keys, pv = param_vector(env)
+        cases[f"c{c}_init"] = np.asarray(init, dtype=np.float64)
+        cases[f"c{c}_params"] = pv
+        cases[f"c{c}_actions"] = actions[: tr["length"]]
+        for k, v in tr.items():
+            cases[f"c{c}_{k}"] = np.asarray(v)
+        lo_s, up_s = env.state_space.bounds
+        cases[f"c{c}_state_lo"], cases[f"c{c}_state_up"] = lo_s, up_s
+        cases[f"c{c}_act_lo"], cases[f"c{c}_act_up"] = lo, up
+        print(f"  {name} case {c}: length {tr['length']}/{H} ret {tr['rews'].sum():.6g} randomized={dp is not None}")
+    cases["n_cases"] = np.array(n_cases)
+    cases["param_keys"] = np.array(keys)
+    cases["dt"] = np.array(env.dt)
+    cases["max_steps"] = np.array(env.max_steps)
+    suffix = "_simple" if kw.get("simple_dynamics") else ""
+    np.savez_compressed(osp.join(OUT, f"traj_{name}{suffix}.npz"), **cases)
+
+
+def gen_fnn_closed_loop():
+    """Config C1: QQubeSwingUpSim(dt=1/250, 600 steps), nominal params, FNN [64,64] tanh on the CPU (upstream
+    semantics: net(obs); the fork's FNNPolicy hard-codes cart-pole features, so the bare FNN module is used),
+    plus the same through ActNormWrapper."""
+    from pyrado.policies.feed_back.fnn import FNN
+
+    out = {}
+    for tag, hidden, wrap in (("h64", [64, 64], False), ("h16_actnorm", [16, 16], True), ("h32", [32, 32], False)):
+        pyrado.set_seed(0)
+        env = QQubeSwingUpSim(dt=1 / 250.0, max_steps=600)
+        net = FNN(input_size=6, output_size=1, hidden_sizes=hidden, hidden_nonlin=torch.tanh)
+        # scale up the output layer so that the closed loop actually moves the pendulum
+        with torch.no_grad():
+            net.output_layer.weight.mul_(8.0)
+        wenv = ActNormWrapper(env) if wrap else env
+        init = env.init_space.sample_uniform()
+        obs = wenv.reset(init_state=init.copy())
+        states, obss, acts, rews = [env.state.copy()], [obs.copy()], [], []
+        done = False
+        while not done:
+            with torch.no_grad():
+                a = net(torch.from_numpy(obs).to(torch.get_default_dtype())).numpy().astype(np.float64)
+            obs, r, done, _ = wenv.step(a)
+            states.append(env.state.copy()); obss.append(obs.copy()); acts.append(a); rews.append(r)
+        params = []
+        for layer in list(net.hidden_layers) + [net.output_layer]:
+            params += [layer.weight.detach().numpy().reshape(-1), layer.bias.detach().numpy().reshape(-1)]
+        out[f"{tag}_weights"] = np.concatenate(params).astype(np.float32)
+        out[f"{tag}_sizes"] = np.array([6] + hidden + [1])
+        out[f"{tag}_init"] = init
+        out[f"{tag}_states"] = np.array(states)
+        out[f"{tag}_obs"] = np.array(obss)
+        out[f"{tag}_acts"] = np.array(acts)
+        out[f"{tag}_rews"] = np.array(rews)
+        out[f"{tag}_actnorm"] = np.array(wrap)
+        print(f"  fnn {tag}: length {len(rews)} ret {np.sum(rews):.6g} max|a| {np.abs(acts).max():.3g}")
+    np.savez_compressed(osp.join(OUT, "fnn_closed_loop_qq.npz"), **out)
+
+
+def gen_policy_forward():
+    """FNN / Linear forward known answers (float32 torch on CPU): fnn.py:138-160, linear.py:95-110, features.py."""
+    from pyrado.policies.feed_back.fnn import FNN
+    from pyrado.policies.features import (FeatureStack, const_feat, identity_feat, squared_feat, sin_feat, cos_feat,
+                                          abs_feat, sign_feat, cubic_feat, sinsin_feat, sincos_feat)
+
+    out = {}
+    torch.manual_seed(7)
+    for tag, (n_in, hidden, n_out) in dict(a=(6, [64, 64], 1), b=(8, [16, 16], 2), c=(5, [32, 32], 1), d=(4, [16], 1)).items():
+        net = FNN(input_size=n_in, output_size=n_out, hidden_sizes=hidden, hidden_nonlin=torch.tanh)
+        x = torch.randn(32, n_in) * 2.0
+        with torch.no_grad():
+            y = net(x)
+        params = []
+        for layer in list(net.hidden_layers) + [net.output_layer]:
+            params += [layer.weight.detach().numpy().reshape(-1), layer.bias.detach().numpy().reshape(-1)]
+        out[f"fnn_{tag}_weights"] = np.concatenate(params).astype(np.float32)
+        out[f"fnn_{tag}_sizes"] = np.array([n_in] + hidden + [n_out])
+        out[f"fnn_{tag}_x"] = x.numpy()
+        out[f"fnn_{tag}_y"] = y.numpy()
+    feats = [const_feat, identity_feat, sign_feat, abs_feat, squared_feat, cubic_feat, sin_feat, cos_feat, sinsin_feat,
+             sincos_feat]
+    names = ["const", "identity", "sign", "abs", "squared", "cubic", "sin", "cos", "sinsin", "sincos"]
+    fs = FeatureStack(*feats)
+    x = torch.randn(16, 4)
+    W = torch.randn(2, fs.get_num_feat(4)) * 0.3
+    with torch.no_grad():
+        y = torch.stack([W @ fs(x[i]) for i in range(x.shape[0])])
+    out["lin_feats"] = np.array(names)
+    out["lin_W"] = W.numpy()
+    out["lin_x"] = x.numpy()
+    out["lin_y"] = y.numpy()
+    np.savez_compressed(osp.join(OUT, "policy_forward.npz"), **out)
+
+
+def gen_qbb_kin():
+    env = QBallBalancerSim(dt=0.01, max_steps=500)
+    rows = []
+    rng = np.random.RandomState(3)
+    for i in range(40):
+        r_arm = 0.0254 * (1 + 0.3 * rng.uniform(-1, 1)) if i % 2 else 0.0254
+        l_plate = 0.275 * (1 + 0.3 * rng.uniform(-1, 1)) if i % 2 else 0.275
+        th = rng.uniform(-np.pi / 2.1, np.pi / 2.1) if i > 0 else 0.0
+        env.domain_param = dict(arm_radius=float(r_arm), plate_length=float(l_plate))
+        ang = env._kin(th)
+        rows.append([r_arm, l_plate, th, ang])
+    np.savez_compressed(osp.join(OUT, "qbb_kin.npz"), rows=np.array(rows))
+    print("  qbb kin: 40 rows")
+
+
+def gen_step_diff():
+    """Config C5 pieces: step_diff_state values and autograd gradients through short horizons (fp64 and fp32)."""
+    out = {}
+    for simple in (False, True):
+        for dtype, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+            torch.set_default_dtype(dtype)
+            env = ObsActCatWrapper(ActNormWrapper(QCartPoleSwingUpSim(dt=1 / 20.0, max_steps=300, long=True,
+                                                                      simple_dynamics=simple, wild_init=True)))
+            inner = env._wrapped_env._wrapped_env
+            rng = np.random.RandomState(11)
+            B, H = 64, 20
+            s0 = rng.uniform(-1, 1, size=(B, 4)) * np.array([0.2, np.pi, 0.5, 2.0])
+            acts = rng.uniform(-1.2, 1.2, size=(H, B, 1))  # normalised; some beyond +-1 (clamped, zero gradient)
+            s0_t = torch.tensor(s0, dtype=dtype, requires_grad=True)
+            a_t = torch.tensor(acts, dtype=dtype, requires_grad=True)
+            # the reference keeps bounds / Q / R as float32 tensors; move them to the working dtype
+            inner._state_space_bound_lo_tensor = inner._state_space_bound_lo_tensor.to(dtype)
+            inner._state_space_bound_up_tensor = inner._state_space_bound_up_tensor.to(dtype)
+            inner.state_des, inner.Q, inner.R = inner.state_des.to(dtype), inner.Q.to(dtype), inner.R.to(dtype)
+            s = s0_t
+            thdd = torch.zeros(B, dtype=dtype)
+            states, rews, dones, thdds = [], [], [], []
+            for t in range(H):
+                s, r, d, info = env.step_diff_state(s, a_t[t], thdd)
+                thdd = info["th_ddot"]
+                states.append(s); rews.append(r); dones.append(d); thdds.append(thdd)
+            total = torch.stack(rews).sum() + 0.1 * s.sum()
+            g_s0, g_a = torch.autograd.grad(total, [s0_t, a_t])
+            key = f"{'simple' if simple else 'full'}_{tag}"
+            out[f"{key}_s0"] = s0
+            out[f"{key}_acts"] = acts
+            out[f"{key}_states"] = torch.stack(states).detach().numpy()
+            out[f"{key}_rews"] = torch.stack(rews).detach().numpy()
+            out[f"{key}_dones"] = torch.stack(dones).numpy()
+            out[f"{key}_thdd"] = torch.stack(thdds).detach().numpy()
+            out[f"{key}_g_s0"] = g_s0.numpy()
+            out[f"{key}_g_a"] = g_a.numpy()
+            # one-step Jacobians d(next_state, rew)/d(state, act) for the first 8 envs
+            s1 = torch.tensor(s0[:8], dtype=dtype, requires_grad=True)
+            a1 = torch.tensor(acts[0, :8], dtype=dtype, requires_grad=True)
+            ns, r, d, info = env.step_diff_state(s1, a1, torch.zeros(8, dtype=dtype))
+            jac = np.zeros((8, 5, 5))
+            for i in range(4):
+                gs, ga = torch.autograd.grad(ns[:, i].sum(), [s1, a1], retain_graph=True)
+                jac[:, i, :4], jac[:, i, 4] = gs.numpy(), ga.numpy()[:, 0]
+            gs, ga = torch.autograd.grad(r.sum(), [s1, a1])
+            jac[:, 4, :4], jac[:, 4, 4] = gs.numpy(), ga.numpy()[:, 0]
+            out[f"{key}_jac"] = jac
+            print(f"  step_diff {key}: ret {float(torch.stack(rews).sum()):.6g} |g_s0| {np.abs(g_s0.numpy()).max():.4g}")
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(osp.join(OUT, "step_diff_qcp.npz"), **out)
+
+
+def gen_dr_moments():
+    """Reference DR draws (torch MT stream, float32): only moments/clip behaviour can be compared with the Philox
+    engine; the raw draws are stored to pin the dtype/clipping conventions (domain_parameter.py:104-132)."""
+    out = {}
+    for name, fn in RANDOMIZERS.items():
+        pyrado.set_seed(0)
+        rz = fn()
+        rz.randomize(2000)
+        d = rz.get_params(-1, fmt="dict", dtype="numpy")
+        out[f"{name}_keys"] = np.array(list(d.keys()))
+        out[f"{name}_mean"] = np.array([np.mean(np.array(v, dtype=np.float64)) for v in d.values()])
+        out[f"{name}_std"] = np.array([np.std(np.array(v, dtype=np.float64)) for v in d.values()])
+        out[f"{name}_min"] = np.array([np.min(np.array(v, dtype=np.float64)) for v in d.values()])
+        out[f"{name}_max"] = np.array([np.max(np.array(v, dtype=np.float64)) for v in d.values()])
+        out[f"{name}_dtype"] = np.array(str(np.asarray(list(d.values())[0][0]).dtype))
+        # distribution table as the reference defines it
+        rows = []
+        for dp in rz.domain_params:
+            kind = type(dp).__name__
+            if kind == "NormalDomainParam":
+                rows.append([0, dp.mean, dp.std, 0.0, dp.clip_lo, dp.clip_up])
+            elif kind == "UniformDomainParam":
+                rows.append([1, dp.mean - dp.halfspan, dp.mean + dp.halfspan, 0.0, dp.clip_lo, dp.clip_up])
+        out[f"{name}_table"] = np.array(rows, dtype=np.float64)
+    np.savez_compressed(osp.join(OUT, "dr_reference.npz"), **out)
+    print("  dr moments written")
+
+
+if __name__ == "__main__":
+    print("trajectories")
+    gen_env_trajs("qq-su", n_cases=6)
+    gen_env_trajs("qcp-su", n_cases=6)
+    gen_env_trajs("qcp-su", n_cases=4, simple_dynamics=True)
+    gen_env_trajs("qbb", n_cases=6)
+    gen_env_trajs("qbb", n_cases=2, simple_dynamics=True)
+    gen_env_trajs("bob", n_cases=6)
+    gen_env_trajs("omo", n_cases=6)
+    print("closed loop"); gen_fnn_closed_loop()
+    print("policies"); gen_policy_forward()
+    print("qbb kin"); gen_qbb_kin()
+    print("step diff"); gen_step_diff()
+    print("dr"); gen_dr_moments()
+    sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
+    print(f"golden size: {sz / 1e6:.2f} MB")
