@@ -104,6 +104,7 @@ def lib():
         L.orc_set_task.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_uint,
                                    C.c_int, C.c_double]
         L.orc_get_spaces.argtypes = [C.c_void_p] * 5
+        L.orc_set_radial_mod.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_get_cmax.restype = C.c_double
         L.orc_get_cmax.argtypes = [C.c_void_p]
         L.orc_get_state.argtypes = [C.c_void_p] * 3
@@ -238,6 +239,11 @@ class OracleEnv:
         Q = np.ascontiguousarray(Q, dtype=np.float64)
         R = np.ascontiguousarray(R, dtype=np.float64)
         self._L.orc_set_task(self._h, _p(sd), _p(Q), _p(R), rew_kind, min_rew, radial_mask, final_flags, final_factor)
+
+    def set_radial_mod(self, mod):
+        m = np.ascontiguousarray(mod, dtype=np.float64)
+        assert m.size == self.d["ds"]
+        self._L.orc_set_radial_mod(self._h, _p(m))
 
     def spaces(self):
         ds, da = self.d["ds"], self.d["da"]

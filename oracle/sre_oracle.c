@@ -79,7 +79,8 @@ typedef struct {
     double R[ORC_MAX_DA * ORC_MAX_DA];
     int rew_kind;
     double min_rew, c_max;
-    unsigned radial_mask; /* bit i set: state index i is modulated by 2*pi (tasks/desired_state.py:146) */
+    unsigned radial_mask; /* bit i set: state index i is modulated (tasks/desired_state.py:146) */
+    double radial_mod[ORC_MAX_DS]; /* modulation factor per state index, default 2*pi (desired_state.py:127,144) */
     int final_flags;
     double final_factor;
     int yielded_final;
@@ -241,6 +242,7 @@ static void orc_default_task(orc_env *e) {
     memset(e->Q, 0, sizeof e->Q);
     memset(e->R, 0, sizeof e->R);
     e->radial_mask = 0; e->final_flags = 0; e->final_factor = 0.0; e->min_rew = 1e-4; e->c_max = 1.0;
+    for (int i = 0; i < ORC_MAX_DS; i++) e->radial_mod[i] = 2 * M_PI;
     double q[ORC_MAX_DS] = {0}, r[ORC_MAX_DA] = {0};
     switch (e->kind) {
     case ORC_QQ:
@@ -293,6 +295,10 @@ void orc_set_task(orc_env *e, const double *state_des, const double *Q, const do
     e->final_flags = final_flags; e->final_factor = fabs(final_factor); /* final_reward.py:99 */
     orc_update_cmax(e);
 }
+
+/* per-index modulation factors of RadiallySymmDesStateTask (desired_state.py:127,144); entries for indices
+ * outside radial_mask are ignored */
+void orc_set_radial_mod(orc_env *e, const double *mod) { memcpy(e->radial_mod, mod, sizeof(double) * k_ds[e->kind]); }
 
 void orc_get_spaces(const orc_env *e, double *st_lo, double *st_up, double *act_lo, double *act_up) {
     memcpy(st_lo, e->st_lo, sizeof(double) * k_ds[e->kind]);
@@ -398,7 +404,7 @@ double orc_step_rew(const orc_env *e, const double *state, const double *act) {
     for (int i = 0; i < ds; i++) err[i] = e->state_des[i] - state[i];
     if (e->radial_mask) {
         for (int i = 0; i < ds; i++)
-            if (e->radial_mask & (1u << i)) err[i] = fmod(err[i], 2 * M_PI);
+            if (e->radial_mask & (1u << i)) err[i] = fmod(err[i], e->radial_mod[i]);
         /* applied to EVERY element, sequentially (desired_state.py:152-153) */
         for (int i = 0; i < ds; i++)
             if (err[i] > M_PI) err[i] = 2 * M_PI - err[i];

@@ -1,0 +1,47 @@
+"""
+Test configuration.  `-m "not gpu"` covers the oracle against the golden vectors, the host-side logic and the
+C-ABI export list; `-m gpu` holds the parity tests proper (they call the CUDA engine through the C-ABI).
+"""
+import os
+import os.path as osp
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = osp.dirname(osp.dirname(osp.abspath(__file__)))
+for p in (ROOT, osp.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = osp.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def golden(name):
+    return np.load(osp.join(GOLDEN, name + ".npz"), allow_pickle=True)
+
+
+@pytest.fixture(scope="session")
+def orc():
+    import oracle as O
+
+    O.build()
+    return O
+
+
+ENV_FILES = [
+    # (golden file, kind name, ctor kwargs of the oracle env)
+    ("traj_qq-su", "qq-su", {}),
+    ("traj_qcp-su", "qcp-su", dict(long_pole=True)),
+    ("traj_qcp-su_simple", "qcp-su", dict(long_pole=True, simple_dynamics=True)),
+    ("traj_qbb", "qbb", {}),
+    ("traj_qbb_simple", "qbb", dict(simple_dynamics=True)),
+    ("traj_bob", "bob", {}),
+    ("traj_omo", "omo", {}),
+]
+
+OMO_TASK = dict(state_des=[0.5, 0.0], Q=np.diag([1e1, 1e-2]), R=np.diag([1e-6]))
