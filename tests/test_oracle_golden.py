@@ -161,7 +161,7 @@ def test_rollout_batch_deterministic_and_split_invariant(orc):
     g = golden("dr_reference")
     table = g["qq-su_table"]
     keys = [str(k) for k in g["qq-su_keys"]]
-    names = ["g", "Rm", "km", "Mr", "Lr", "Dr", "Mp", "Lp", "Dp", "V_thold_neg", "V_thold_pos"]
+    names = [str(k) for k in golden("traj_qq-su")["param_keys"]]
     ent = [dict(param_index=names.index(k), kind="normal", a=r[1], b=r[2], clip_lo=r[4], clip_up=r[5])
            for k, r in zip(keys, table)]
     arr = orc.make_distr_table(ent)
