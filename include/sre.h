@@ -1,0 +1,294 @@
+/*
+ * sre.h -- C-ABI of the B200-native batched rollout engine for Pyrado's pysim environments.
+ *
+ * The reference (swami1995/SimuRLacra) has NO FFI on this path: pysim envs are plain Python classes
+ * and the boundary is the duck-typed Env API.  This header is therefore the boundary a maintainer would
+ * bind (ctypes) UNDER Python classes that keep the reference signatures.  Each entry
+ * point cites the reference interface it replaces; paths are relative to /root/reference/Pyrado/pyrado/ .
+ *
+ * Conventions
+ *   - every function returns int: 0 = ok, < 0 = argument error (SRE_E_*), > 0 = CUDA error code;
+ *     sre_last_error() gives a thread-local message for the last non-zero return
+ *   - "real" arrays are float (cfg.dtype == SRE_F32) or double (SRE_F64); policy weights are always float
+ *   - all data pointers are DEVICE pointers owned by the caller unless the parameter says "host"
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the default stream); calls are asynchronous
+ *   - nothing crosses the ABI but plain pointers, sizes and the POD structs below; no torch types
+ *   - there is no CPU fallback: without a CUDA device every compute call returns a CUDA error
+ */
+#ifndef SRE_H
+#define SRE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden; only this header is exported */
+#endif
+
+#define SRE_ABI_VERSION 1
+
+/* environment kinds (environments/pysim/*.py) */
+#define SRE_QQ 0  /* QQubeSwingUpSim       quanser_qube.py:152 */
+#define SRE_QCP 1 /* QCartPoleSwingUpSim   quanser_cartpole.py:507 */
+#define SRE_QBB 2 /* QBallBalancerSim      quanser_ball_balancer.py:50 */
+#define SRE_BOB 3 /* BallOnBeamSim         ball_on_beam.py:41 */
+#define SRE_OMO 4 /* OneMassOscillatorSim  one_mass_oscillator.py:43 */
+#define SRE_N_KINDS 5
+
+#define SRE_F32 0
+#define SRE_F64 1
+
+#define SRE_MAX_DS 8
+#define SRE_MAX_DO 8
+#define SRE_MAX_DA 2
+#define SRE_MAX_DP 20
+#define SRE_MAX_NH 2
+#define SRE_MAX_DISTR 32
+#define SRE_MAX_LAYERS 8
+#define SRE_MAX_WIDTH 128
+#define SRE_MAX_FEATS 12
+
+/* cfg.flags */
+#define SRE_F_SIMPLE_DYN 1 /* simple_dynamics=True (quanser_cartpole.py:515, quanser_ball_balancer.py:64) */
+
+/* reward kinds: tasks/reward_functions.py:176 (Quadr), :224 (ExpQuadr), :247 (ScaledExpQuadr) */
+#define SRE_REW_QUADR 0
+#define SRE_REW_EXP 1
+#define SRE_REW_SCALED_EXP 2
+
+/* FinalRewMode bits: tasks/final_reward.py:41-48 */
+#define SRE_FR_ENABLED 1
+#define SRE_FR_STATE_DEP 2
+#define SRE_FR_TIME_DEP 4
+#define SRE_FR_ALWAYS_POS 8
+#define SRE_FR_ALWAYS_NEG 16
+
+/* policy kinds */
+#define SRE_POL_ACTIONS 0 /* injected actions [H, N, da] */
+#define SRE_POL_FNN 1     /* policies/feed_back/fnn.py:43 (FNN), :163 (FNNPolicy) */
+#define SRE_POL_LINEAR 2  /* policies/feed_back/linear.py:41 + policies/features.py:42 */
+#define SRE_POL_IDLE 3    /* policies/feed_forward/dummy.py (IdlePolicy): zero action */
+
+/* feature functions of the Linear policy, policies/features.py:127-175 */
+#define SRE_FEAT_CONST 0
+#define SRE_FEAT_IDENTITY 1
+#define SRE_FEAT_SIGN 2
+#define SRE_FEAT_ABS 3
+#define SRE_FEAT_SQUARED 4
+#define SRE_FEAT_CUBIC 5
+#define SRE_FEAT_SIN 6
+#define SRE_FEAT_COS 7
+#define SRE_FEAT_SINSIN 8
+#define SRE_FEAT_SINCOS 9
+
+/* distribution kinds, domain_randomization/domain_parameter.py:135 (Uniform), :171 (Normal), :246 (Bernoulli) */
+#define SRE_DISTR_NORMAL 0    /* a = mean, b = std */
+#define SRE_DISTR_UNIFORM 1   /* a = lo,   b = hi  */
+#define SRE_DISTR_BERNOULLI 2 /* a = val_0, b = val_1, c = prob_1 */
+
+/* row flags written next to the trajectory records */
+#define SRE_ROW_STEP 0      /* a step was taken from this row, episode continues */
+#define SRE_ROW_DONE 1      /* a step was taken from this row and it ended the episode (done == True) */
+#define SRE_ROW_TERMINAL 2  /* closing row of a finished episode: obs/state/hidden only */
+#define SRE_ROW_TRUNCATED 3 /* closing row of an episode cut by the row budget (not done) */
+#define SRE_ROW_IDLE 4      /* lane idle (single-episode mode, after the closing row): record is zero */
+
+/* per-env status bits (instead of the exceptions the reference raises mid-flight) */
+#define SRE_ST_NAN_STATE 1 /* spaces/box.py:142 would raise ValueErr */
+#define SRE_ST_NAN_ACT 2   /* sampling/rollout.py:223 would raise ValueErr */
+#define SRE_ST_NAN_OBS 4   /* sampling/rollout.py:193 would raise ValueErr */
+
+/* error codes */
+#define SRE_E_ARG (-1)
+#define SRE_E_KIND (-2)
+#define SRE_E_DTYPE (-3)
+#define SRE_E_POLICY (-4)
+#define SRE_E_UNSUPPORTED (-5)
+
+/* rollout statistics vector (doubles), the numbers the NCCL all-reduce carries:
+ * sums first (all-reduce SUM), then min/max */
+#define SRE_STAT_EPISODES 0
+#define SRE_STAT_SUM_RET 1
+#define SRE_STAT_SUM_RET2 2
+#define SRE_STAT_SUM_LEN 3
+#define SRE_STAT_STEPS 4
+#define SRE_STAT_FAILED 5 /* episodes ended by leaving the state space */
+#define SRE_STAT_MIN_RET 6
+#define SRE_STAT_MAX_RET 7
+#define SRE_N_STATS 8
+
+/* Task description: tasks/desired_state.py:40 (DesStateTask), :116 (RadiallySymmDesStateTask),
+ * tasks/final_reward.py:69 (FinalRewTask), reward functions above.  success_fcn is never_succeeded
+ * (tasks/utils.py:32) as in all five pysim envs. */
+typedef struct sre_task {
+    double state_des[SRE_MAX_DS];
+    double Q[SRE_MAX_DS * SRE_MAX_DS]; /* row-major [ds, ds] */
+    double R[SRE_MAX_DA * SRE_MAX_DA]; /* row-major [da, da] */
+    double radial_mod[SRE_MAX_DS];     /* modulation factor per state index (default 2*pi) */
+    double min_rew;                    /* ScaledExpQuadrErrRewFcn.min_rew, reward_functions.py:257 */
+    double final_factor;               /* FinalRewTask factor, final_reward.py:99 */
+    int32_t rew_kind;
+    uint32_t radial_mask;              /* bit i: state index i is modulated (desired_state.py:146) */
+    int32_t final_flags;
+    int32_t reserved;
+} sre_task;
+
+/* One batch of identical environments: ctor arguments of SimPyEnv (environments/pysim/base.py:47) plus the
+ * wrappers that are fused into the kernels. */
+typedef struct sre_env_cfg {
+    int32_t kind;
+    int32_t dtype;
+    int32_t flags;
+    int32_t wild_init; /* QCP init box: 0 -> 'True', 1 -> 'False', 2 -> else (quanser_cartpole.py:552-560) */
+    double dt;
+    int64_t max_steps; /* <= 0: inf */
+    sre_task task;
+    double base_params[SRE_MAX_DP]; /* domain parameters used where no per-env value is given */
+    int32_t act_norm;               /* ActNormWrapper, environment_wrappers/action_normalization.py:66 */
+    int32_t obs_noise;              /* GaussianObsNoiseWrapper, environment_wrappers/observation_noise.py:39 */
+    double noise_std[SRE_MAX_DO];
+    double noise_mean[SRE_MAX_DO];
+    int32_t has_init_box;           /* init_space setter (base.py:99): a box replacing the default init space */
+    int32_t reserved;
+    double init_box_lo[SRE_MAX_DS];
+    double init_box_up[SRE_MAX_DS];
+} sre_env_cfg;
+
+/* DomainParam (domain_randomization/domain_parameter.py:46): float32 sample -> clamp -> optional round */
+typedef struct sre_distr {
+    int32_t param_index;
+    int32_t kind;
+    float a, b, c;
+    float clip_lo, clip_up;
+    int32_t roundint;
+} sre_distr;
+
+typedef struct sre_policy {
+    int32_t kind;
+    int32_t n_layers;                 /* FNN: number of Linear layers (hidden + output) */
+    int32_t sizes[SRE_MAX_LAYERS + 1]; /* FNN: in, h1, ..., out */
+    int32_t n_feats;                  /* Linear: number of feature functions */
+    int32_t feats[SRE_MAX_FEATS];
+    int32_t hidden_nonlin;            /* 0 tanh, 1 relu, 2 identity */
+    int32_t output_nonlin;            /* 0 none, 1 tanh */
+    int32_t cartpole_feats;           /* the fork's FNNPolicy input transform, fnn.py:214-218 */
+    const float *weights;             /* device; torch layout W[out][in], bias[out], layers concatenated */
+    int64_t n_weights;
+} sre_policy;
+
+/* Inputs / outputs of one rollout launch.  Replaces rollout() (sampling/rollout.py:63) run for N envs by
+ * ParallelRolloutSampler.sample (sampling/parallel_rollout_sampler.py:248). */
+typedef struct sre_rollout_io {
+    int64_t n_envs;           /* N (this rank's shard) */
+    int64_t n_rows;           /* T: rows per env lane in `traj`/`row_flag`; a lane takes at most T - 1 steps */
+    uint64_t seed;            /* Philox key */
+    uint64_t env_offset;      /* global index of lane 0 (multi-GPU shard offset) */
+    uint32_t episode;         /* first episode index of every lane */
+    int32_t stop_on_done;     /* rollout(stop_on_done=...) */
+    int32_t auto_reset;       /* 1: a lane starts episode+1 after its closing row (min_steps sampling) */
+    int32_t n_distr;
+    const sre_distr *distr;   /* HOST pointer to n_distr entries, or NULL */
+    const void *params;       /* real [N, dp] or NULL -> cfg.base_params */
+    const void *init;         /* real [N, n_init_cols] or NULL -> sample the init space */
+    int32_t n_init_cols;
+    int32_t reserved;
+    const void *actions;      /* real [T-1, N, da] for SRE_POL_ACTIONS (NULL -> zeros) */
+    /* outputs, any may be NULL */
+    void *traj;               /* real [T, N, W] records, W = sre_record_width(kind) */
+    uint8_t *row_flag;        /* [T, N] SRE_ROW_* */
+    void *ret;                /* real [N]   undiscounted return of the lane's first episode */
+    int32_t *length;          /* [N]        length of the lane's first episode */
+    void *params_out;         /* real [N, dp] parameters of the lane's first episode */
+    double *stats;            /* [SRE_N_STATS] accumulated with atomics; caller initialises (sre_stats_init) */
+    int32_t *status;          /* [N] SRE_ST_* bits */
+} sre_rollout_io;
+
+/* ---- introspection (host only) ---------------------------------------------------------------------- */
+int sre_abi_version(void);
+const char *sre_last_error(void);
+int sre_device_count(int *count);
+/* dims of an env kind: state, obs, act, domain-param, hidden-state, init-space dims (SimPyEnv spaces) */
+int sre_env_dims(int kind, int *ds, int *dobs, int *da, int *dp, int *nh, int *dinit);
+/* get_nominal_domain_param(): quanser_qube.py:54, quanser_cartpole.py:111, quanser_ball_balancer.py:169,
+ * ball_on_beam.py:75, one_mass_oscillator.py:81.  dp: host double[SRE_MAX_DP] */
+int sre_nominal_params(int kind, int long_pole, double *dp);
+/* default task of the env (_create_task): fills cfg->task.  host */
+int sre_default_task(int kind, sre_task *task);
+/* record layout of `traj`: W and the offsets of obs, act, act_app, rew, state, hidden inside a record */
+int sre_record_width(int kind);
+int sre_record_layout(int kind, int *off_obs, int *off_act, int *off_act_app, int *off_rew, int *off_state,
+                      int *off_hidden);
+int sre_stats_init(double *stats, void *stream);
+
+/* ---- domain parameters ------------------------------------------------------------------------------ */
+/* domain_param setter side effects (base.py:112-124): _calc_constants + _create_spaces + ScaledExp c_max.
+ * params real [N, dp]; outputs real: st_lo/st_up [N, ds], act_lo/act_up [N, da], c_max [N]; any may be NULL */
+int sre_derive(const sre_env_cfg *cfg, const void *params, int64_t n, void *st_lo, void *st_up, void *act_lo,
+               void *act_up, void *c_max, void *stream);
+/* DomainRandomizer.randomize + get_params (domain_randomizer.py:123,159) for episode `episode` of envs
+ * env_offset .. env_offset + n - 1: overwrites the listed columns of params real [N, dp]. distr: HOST */
+int sre_sample_params(const sre_env_cfg *cfg, const sre_distr *distr, int n_distr, uint64_t seed,
+                      uint64_t env_offset, uint32_t episode, void *params, int64_t n, void *stream);
+/* init_space.sample_uniform() (spaces/box.py:169, polar.py:108, compound.py:83): init real [N, dinit] */
+int sre_sample_init(const sre_env_cfg *cfg, const void *params, uint64_t seed, uint64_t env_offset,
+                    uint32_t episode, void *init, int64_t n, void *stream);
+
+/* ---- step-granular API: SimPyEnv.reset / step (base.py:166, :217) ------------------------------------- */
+/* mask: uint8 [N] or NULL (all).  init real [N, n_init_cols] (n_init_cols == ds: full state, else init space).
+ * Writes state [N, ds], hidden [N, max(nh,1)], curr_step int32 [N], obs [N, do] (obs may be NULL).
+ * seed/env_offset/episode key the observation noise when cfg.obs_noise (Philox block t = 0). */
+int sre_reset(const sre_env_cfg *cfg, const void *params, const void *init, int n_init_cols, const uint8_t *mask,
+              void *state, void *hidden, int32_t *curr_step, void *obs, uint64_t seed, uint64_t env_offset,
+              uint32_t episode, int64_t n, void *stream);
+/* act real [N, da] in the units of the outermost fused wrapper (normalised if cfg.act_norm).
+ * Updates state/hidden/curr_step in place; writes obs [N, do], rew [N], done uint8 [N], status int32 [N].
+ * noise_seed/env_offset/episode key the observation noise when cfg.obs_noise. */
+int sre_step(const sre_env_cfg *cfg, const void *params, const void *act, void *state, void *hidden,
+             int32_t *curr_step, void *obs, void *rew, uint8_t *done, int32_t *status, uint64_t seed,
+             uint64_t env_offset, uint32_t episode, int64_t n, void *stream);
+/* Env.observe (environments/base.py:203 and the overrides): obs [N, do] from state [N, ds] */
+int sre_observe(const sre_env_cfg *cfg, const void *state, void *obs, int64_t n, void *stream);
+/* Policy.forward for a batch: obs float [N, n_obs] -> act float [N, n_act] (always float32) */
+int sre_policy_forward(const sre_policy *pol, const float *obs, int n_obs, float *act, int n_act, int64_t n,
+                       void *stream);
+
+/* ---- persistent-horizon rollout ----------------------------------------------------------------------- */
+int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout_io *io, void *stream);
+/* number of kernels the last sre_rollout call on this thread launched (for bench.py's gpu_launches) */
+int sre_last_launch_count(void);
+
+/* ---- differentiable cart-pole step (quanser_cartpole.py:257-358, state_based=True) ------------------- */
+/* Forward over a horizon with injected actions.  act real [H, N] in inner-env units BEFORE the clamp
+ * (act + act_diff of step_diff_state); s0 real [N, 4]; thdd0 real [N] or NULL (zeros).
+ * Outputs: states real [H+1, N, 4] (row 0 = s0), thdd real [H+1, N] (carry before each step), rew real [H, N],
+ * done uint8 [H, N].  states/thdd are the tape the backward pass reads. */
+int sre_qcp_diff_forward(const sre_env_cfg *cfg, const void *params, const void *s0, const void *thdd0,
+                         const void *act, int64_t n, int64_t horizon, void *states, void *thdd, void *rew,
+                         uint8_t *done, void *stream);
+/* Adjoint through the horizon.  Inputs: the tape, g_states real [H+1, N, 4] (dL/d states, row 0 = dL/d s0
+ * direct term), g_rew real [H, N], g_thdd real [H+1, N] or NULL.  Outputs: g_s0 real [N, 4], g_act real [H, N],
+ * g_thdd0 real [N] (may be NULL). */
+int sre_qcp_diff_backward(const sre_env_cfg *cfg, const void *params, const void *states, const void *thdd,
+                          const void *act, const void *g_states, const void *g_rew, const void *g_thdd,
+                          int64_t n, int64_t horizon, void *g_s0, void *g_act, void *g_thdd0, void *stream);
+/* Per-step Jacobians d(next_state, rew)/d(state, act): jac real [N, 5, 5] (rows s'0..3, rew; cols s0..3, act),
+ * the quantities rollout_tensor_full collects (sampling/rollout.py:832-837). */
+int sre_qcp_diff_jacobian(const sre_env_cfg *cfg, const void *params, const void *state, const void *thdd,
+                          const void *act, int64_t n, void *jac, void *stream);
+
+/* ---- measurement helpers (roofline denominators measured on the box) ---------------------- */
+/* FMA-only kernel: every thread runs `iters` x 32 dependent-free FFMA (dtype F32) or DFMA (F64).
+ * Returns FLOPs issued in *flops; time it with CUDA events on `stream`. */
+int sre_bench_fma(int dtype, int64_t iters, int blocks, int threads, float *sink, double *flops, void *stream);
+/* streaming write of `bytes` with 128-bit stores (the HBM-write denominator) */
+int sre_bench_hbm_write(void *dst, int64_t bytes, void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRE_H */

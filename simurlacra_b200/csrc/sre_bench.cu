@@ -1,0 +1,52 @@
+// sre_bench.cu -- measurement helpers: the roofline denominators are MEASURED on the box, because
+// MEASURED_PEAKS.json has no FP32/FP64 FMA figure.  bench.py times these launches with CUDA events.
+#include "sre_host.h"
+
+namespace sre {
+
+// 32 independent accumulator chains per thread: no dependency stalls, no memory traffic
+template <typename R> __global__ void __launch_bounds__(256) fma_kernel(long long iters, R seed, R *sink) {
+    R acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc[i] = seed + (R)(threadIdx.x + i);
+    const R a = (R)1.0000001, b = (R)1e-7;
+    for (long long it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 32; i++) acc[i] = acc[i] * a + b;
+    }
+    R s = (R)0;
+#pragma unroll
+    for (int i = 0; i < 32; i++) s += acc[i];
+    if (s == (R)123.456) sink[0] = s;  // keeps the loop alive, never true in practice
+}
+
+__global__ void __launch_bounds__(256) hbm_write_kernel(float4 *dst, long long n_vec) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const float4 v = make_float4(1.f, 2.f, 3.f, 4.f);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) __stcs(dst + i, v);
+}
+
+}  // namespace sre
+
+using namespace sre;
+
+extern "C" {
+
+int sre_bench_fma(int dtype, int64_t iters, int blocks, int threads, float *sink, double *flops, void *stream) {
+    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64, SRE_E_DTYPE, "unknown dtype %d", dtype);
+    SRE_CHECK_ARG(iters > 0 && blocks > 0 && threads > 0 && threads <= 256 && sink, SRE_E_ARG, "bad launch shape");
+    if (dtype == SRE_F32) fma_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
+    else fma_kernel<double><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5, reinterpret_cast<double *>(sink));
+    if (flops) *flops = 2.0 * 32.0 * (double)iters * (double)blocks * (double)threads;
+    SRE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int sre_bench_hbm_write(void *dst, int64_t bytes, void *stream) {
+    SRE_CHECK_ARG(dst && bytes >= 16 && (reinterpret_cast<size_t>(dst) % 16) == 0, SRE_E_ARG, "bad buffer");
+    hbm_write_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4 *>(dst), bytes / 16);
+    SRE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

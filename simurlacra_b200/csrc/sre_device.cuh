@@ -1,0 +1,129 @@
+// sre_device.cuh -- device-side building blocks shared by all kernels: math wrappers templated on the real
+// type (float = production build, double = verification build), Philox4x32-10 and the sample mappings of the
+// engine's RNG specification (restated independently in oracle/sre_oracle.c, pinned by the Random123 vectors).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sre.h"
+
+#define SRE_DEV __device__ __forceinline__
+#define SRE_PI 3.14159265358979323846
+
+namespace sre {
+
+// ------------------------------------------------------------------------------------------------------
+// math: one overload set per real type, so that the env code reads like the reference's formulas
+// ------------------------------------------------------------------------------------------------------
+SRE_DEV float m_sin(float x) { return sinf(x); }
+SRE_DEV double m_sin(double x) { return sin(x); }
+SRE_DEV float m_cos(float x) { return cosf(x); }
+SRE_DEV double m_cos(double x) { return cos(x); }
+SRE_DEV void m_sincos(float x, float &s, float &c) { sincosf(x, &s, &c); }
+SRE_DEV void m_sincos(double x, double &s, double &c) { sincos(x, &s, &c); }
+SRE_DEV float m_exp(float x) { return expf(x); }
+SRE_DEV double m_exp(double x) { return exp(x); }
+SRE_DEV float m_log(float x) { return logf(x); }
+SRE_DEV double m_log(double x) { return log(x); }
+SRE_DEV float m_sqrt(float x) { return sqrtf(x); }
+SRE_DEV double m_sqrt(double x) { return sqrt(x); }
+SRE_DEV float m_fmod(float x, float y) { return fmodf(x, y); }
+SRE_DEV double m_fmod(double x, double y) { return fmod(x, y); }
+SRE_DEV float m_abs(float x) { return fabsf(x); }
+SRE_DEV double m_abs(double x) { return fabs(x); }
+SRE_DEV float m_min(float x, float y) { return fminf(x, y); }
+SRE_DEV double m_min(double x, double y) { return fmin(x, y); }
+SRE_DEV float m_max(float x, float y) { return fmaxf(x, y); }
+SRE_DEV double m_max(double x, double y) { return fmax(x, y); }
+SRE_DEV float m_floor(float x) { return floorf(x); }
+SRE_DEV double m_floor(double x) { return floor(x); }
+template <typename R> SRE_DEV R m_sign(R x) { return (R)((x > (R)0) - (x < (R)0)); }
+template <typename R> SRE_DEV bool m_isnan(R x) { return x != x; }
+
+// ------------------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11; Random123 constants)
+// Engine addressing: key = (seed_lo, seed_hi); counter = (env_lo, env_hi, episode, stream << 24 | block)
+// ------------------------------------------------------------------------------------------------------
+#define SRE_STREAM_PARAMS 0u
+#define SRE_STREAM_INIT 1u
+#define SRE_STREAM_OBS_NOISE 2u
+#define SRE_STREAM_ACT_NOISE 3u
+
+struct u32x4 {
+    uint32_t x, y, z, w;
+};
+
+SRE_DEV u32x4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return u32x4{c0, c1, c2, c3};
+}
+
+SRE_DEV u32x4 rng_block(uint64_t seed, uint64_t env, uint32_t episode, uint32_t stream, uint32_t block) {
+    return philox4x32_10((uint32_t)env, (uint32_t)(env >> 32), episode, (stream << 24) | (block & 0xFFFFFFu),
+                         (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
+// numpy-style 53-bit uniform in [0, 1)
+SRE_DEV double u53(uint32_t a, uint32_t b) {
+    return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) * (1.0 / 9007199254740992.0);
+}
+SRE_DEV float u24(uint32_t a) { return (float)(a >> 8) * (1.0f / 16777216.0f); }
+// Box-Muller in fp64 (once per episode and parameter: accuracy matters more than speed)
+SRE_DEV double normal_d(uint32_t a, uint32_t b) {
+    double u1 = ((double)a + 1.0) * (1.0 / 4294967296.0);
+    double u2 = (double)b * (1.0 / 4294967296.0);
+    return sqrt(-2.0 * log(u1)) * cos(2.0 * SRE_PI * u2);
+}
+
+// DomainParam.sample for one table entry (domain_parameter.py:104-132): float32 draw like torch's default
+// dtype -> clamp -> optional round.  Separate roundings (no FMA contraction): loc + scale * eps.
+SRE_DEV float sample_entry(const sre_distr &d, uint64_t seed, uint64_t env, uint32_t episode, uint32_t entry) {
+    u32x4 x = rng_block(seed, env, episode, SRE_STREAM_PARAMS, entry);
+    float s;
+    if (d.kind == SRE_DISTR_NORMAL) {
+        float z = (float)normal_d(x.x, x.y);
+        s = __fadd_rn(d.a, __fmul_rn(d.b, z));
+    } else if (d.kind == SRE_DISTR_UNIFORM) {
+        float u = u24(x.x);
+        s = __fadd_rn(d.a, __fmul_rn(u, __fsub_rn(d.b, d.a)));
+    } else {
+        float u = u24(x.x);
+        float bern = (u < d.c) ? 1.0f : 0.0f;
+        s = __fadd_rn(__fmul_rn(1.0f - bern, d.a), __fmul_rn(bern, d.b));
+    }
+    s = fminf(fmaxf(s, d.clip_lo), d.clip_up);
+    if (d.roundint) s = rintf(s);
+    return s;
+}
+
+// four standard normals from one Philox block (two Box-Muller pairs), observation / action noise
+template <typename R> SRE_DEV void normal4(const u32x4 &x, R z[4]);
+template <> SRE_DEV void normal4<double>(const u32x4 &x, double z[4]) {
+    double u1 = ((double)x.x + 1.0) / 4294967296.0, u2 = (double)x.y / 4294967296.0;
+    double u3 = ((double)x.z + 1.0) / 4294967296.0, u4 = (double)x.w / 4294967296.0;
+    double r1 = sqrt(-2 * log(u1)), r2 = sqrt(-2 * log(u3));
+    double s1, c1, s2, c2;
+    sincospi(2.0 * u2, &s1, &c1);
+    sincospi(2.0 * u4, &s2, &c2);
+    z[0] = r1 * c1; z[1] = r1 * s1; z[2] = r2 * c2; z[3] = r2 * s2;
+}
+template <> SRE_DEV void normal4<float>(const u32x4 &x, float z[4]) {
+    // same uniforms as the fp64 form, rounded to float (u1 in (0, 1], u2 in [0, 1])
+    const float k = 1.0f / 4294967296.0f;
+    float u1 = ((float)x.x + 1.0f) * k, u2 = (float)x.y * k;
+    float u3 = ((float)x.z + 1.0f) * k, u4 = (float)x.w * k;
+    float r1 = sqrtf(-2.0f * logf(u1)), r2 = sqrtf(-2.0f * logf(u3));
+    float s1, c1, s2, c2;
+    sincospif(2.0f * u2, &s1, &c1);
+    sincospif(2.0f * u4, &s2, &c2);
+    z[0] = r1 * c1; z[1] = r1 * s1; z[2] = r2 * c2; z[3] = r2 * s2;
+}
+
+}  // namespace sre

@@ -1,0 +1,353 @@
+// sre_rollout.cuh -- the persistent-horizon rollout kernel: one thread owns one environment lane for the whole
+// launch.  Replaces the hot loop of rollout() (sampling/rollout.py:185-312) run for N envs by
+// ParallelRolloutSampler.sample (sampling/parallel_rollout_sampler.py:248-323):
+//   per lane: [DR sample] -> reset -> loop { obs (+noise) -> policy (fp32) -> [ActNorm] -> SimPyEnv.step } -> closing row
+// State, derived constants and policy activations stay in registers; policy weights sit in shared memory;
+// trajectory rows are staged per warp in shared memory and written with 128-bit coalesced stores.
+#pragma once
+#include "sre_core.cuh"
+#include "sre_policy.cuh"
+
+namespace sre {
+
+// policy variants compiled per (env, dtype)
+#define SRE_PV_ACTIONS 0  // injected actions or idle
+#define SRE_PV_GENERIC 1  // generic FNN
+#define SRE_PV_LINEAR 2
+#define SRE_PV_FNN16 16
+#define SRE_PV_FNN32 32
+#define SRE_PV_FNN64 64
+
+struct KIO {
+    long long n_envs, n_rows;
+    unsigned long long seed, env_offset;
+    unsigned episode;
+    int stop_on_done, auto_reset;
+    const void *params, *init, *actions;
+    int n_init_cols;
+    void *traj;
+    unsigned char *row_flag;
+    void *ret;
+    int *length;
+    void *params_out;
+    double *stats;
+    int *status;
+    int idle_policy;
+};
+
+template <int KIND, typename R> struct Rec {
+    using E = Env<KIND, R>;
+    static constexpr int OFF_OBS = 0;
+    static constexpr int OFF_ACT = E::DO;
+    static constexpr int OFF_ACT_APP = OFF_ACT + E::DA;
+    static constexpr int OFF_REW = OFF_ACT_APP + E::DA;
+    static constexpr int OFF_STATE = OFF_REW + 1;
+    static constexpr int OFF_HIDDEN = OFF_STATE + E::DS;
+    static constexpr int W = OFF_HIDDEN + E::NH;
+};
+
+// cooperative store of one warp's row tile: n_valid contiguous reals from shared to global memory
+template <typename R> SRE_DEV void warp_store_row(const R *stage, R *g, int n_valid, bool vec_ok, int lane) {
+    constexpr int V = 16 / sizeof(R);
+    if (vec_ok) {
+        const int nv = n_valid / V;
+        const float4 *s4 = reinterpret_cast<const float4 *>(stage);
+        float4 *g4 = reinterpret_cast<float4 *>(g);
+        for (int i = lane; i < nv; i += 32) __stcs(g4 + i, s4[i]);  // streaming: written once, not re-read here
+        for (int i = nv * V + lane; i < n_valid; i += 32) g[i] = stage[i];
+    } else {
+        for (int i = lane; i < n_valid; i += 32) g[i] = stage[i];
+    }
+}
+
+SRE_DEV void atomic_min_double(double *addr, double v) {
+    unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) <= v) break;
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    } while (assumed != old);
+}
+SRE_DEV void atomic_max_double(double *addr, double v) {
+    unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) >= v) break;
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    } while (assumed != old);
+}
+
+template <int KIND, typename R, int PV>
+__global__ void __launch_bounds__(128)
+rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDistr distr,
+               const __grid_constant__ KPolicy pol, const __grid_constant__ KIO io) {
+    using E = Env<KIND, R>;
+    using RC = Rec<KIND, R>;
+    constexpr int DS = E::DS, DO = E::DO, DA = E::DA, DP = E::DP, NH = E::NH, W = RC::W;
+    using Fast = FnnFast<DO, (PV >= 16 ? PV : 16), DA>;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *sm_w = reinterpret_cast<float *>(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
+
+    if (PV >= 16) Fast::stage(pol.weights, sm_w);
+    else if (PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) stage_generic(pol, sm_w);
+    __syncthreads();
+
+    const long long N = io.n_envs;
+    const long long T = io.n_rows;
+    const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long warp_env0 = n - lane;
+    const bool valid = n < N;
+    const uint64_t genv = io.env_offset + (uint64_t)n;
+    const int n_valid_lanes = (int)min((long long)32, max((long long)0, N - warp_env0));
+    const bool vec_ok = ((N * W * (long long)sizeof(R)) % 16 == 0) && ((reinterpret_cast<size_t>(io.traj) % 16) == 0);
+    const bool record = io.traj != nullptr;
+
+    enum { RUN = 0, CLOSING = 1, IDLE = 2 };
+    Lane<KIND, R> L;
+    R dp[DP];
+    R obs[DO];
+    uint32_t episode = io.episode;
+    int lane_state = valid ? RUN : IDLE;
+    int t_ep = 0;
+    R ret_ep = (R)0;
+    bool first_episode = true;
+    bool failed_ep = false;
+    int status = 0;
+    // statistics over completed episodes of this lane
+    double st_eps = 0, st_ret = 0, st_ret2 = 0, st_len = 0, st_steps = 0, st_failed = 0;
+    double st_min = 1e300, st_max = -1e300;
+
+    auto start_episode = [&]() {
+#pragma unroll
+        for (int i = 0; i < DP; i++)
+            dp[i] = io.params ? static_cast<const R *>(io.params)[n * DP + i] : cfg.base_params[i];
+        // DomainRandWrapperLive.reset (environment_wrappers/domain_randomization.py:141-148)
+        for (int i = 0; i < distr.n; i++) {
+            const float v = sample_entry(distr.e[i], io.seed, genv, episode, (uint32_t)i);
+            const int pi = distr.e[i].param_index;
+#pragma unroll
+            for (int j = 0; j < DP; j++)
+                if (j == pi) dp[j] = (R)v;  // static register indexing
+        }
+        L.set_params(cfg, dp);
+        if (first_episode && io.params_out) {
+#pragma unroll
+            for (int i = 0; i < DP; i++) static_cast<R *>(io.params_out)[n * DP + i] = dp[i];
+        }
+        R init[DS];
+        int n_cols = E::DINIT;
+        if (io.init) {
+            n_cols = io.n_init_cols;
+#pragma unroll
+            for (int i = 0; i < DS; i++)
+                if (i < n_cols) init[i] = static_cast<const R *>(io.init)[n * n_cols + i];
+        } else {
+            sample_init<KIND, R>(cfg, dp, io.seed, genv, episode, init);
+        }
+        L.reset(cfg, dp, init, n_cols);
+        E::observe(L.s, obs);
+        t_ep = 0;
+        ret_ep = (R)0;
+        failed_ep = false;
+    };
+    auto finish_episode = [&](bool complete) {
+        if (first_episode) {
+            if (io.ret) static_cast<R *>(io.ret)[n] = ret_ep;
+            if (io.length) io.length[n] = t_ep;
+            first_episode = false;
+        }
+        if (complete) {
+            st_eps += 1;
+            st_ret += (double)ret_ep;
+            st_ret2 += (double)ret_ep * (double)ret_ep;
+            st_len += t_ep;
+            st_failed += failed_ep ? 1 : 0;
+            st_min = fmin(st_min, (double)ret_ep);
+            st_max = fmax(st_max, (double)ret_ep);
+        }
+    };
+
+    if (valid) start_episode();
+
+    for (long long row = 0; row < T; row++) {
+        R rec[W];
+#pragma unroll
+        for (int i = 0; i < W; i++) rec[i] = (R)0;
+        unsigned char flag = SRE_ROW_IDLE;
+
+        if (lane_state == RUN && row < T - 1) {
+            if (cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
+            // ---- policy (float32) ----
+            R act[DA];
+            if (PV == SRE_PV_ACTIONS) {
+#pragma unroll
+                for (int i = 0; i < DA; i++)
+                    act[i] = (io.actions && !io.idle_policy)
+                                 ? static_cast<const R *>(io.actions)[(row * N + n) * DA + i]
+                                 : (R)0;
+            } else {
+                float of[DO], af[DA];
+#pragma unroll
+                for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
+                if (PV >= 16) Fast::forward(sm_w, of, af);
+                else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
+                else linear_forward<DO, DA>(pol, sm_w, of, af);
+#pragma unroll
+                for (int i = 0; i < DA; i++) act[i] = (R)af[i];
+            }
+            // ---- wrappers: ActNormWrapper._process_act (action_normalization.py:69-75) ----
+            R act_env[DA];
+#pragma unroll
+            for (int i = 0; i < DA; i++) {
+                act_env[i] = cfg.act_norm ? L.act_lo[i] + (act[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2 : act[i];
+                if (m_isnan(act[i])) status |= SRE_ST_NAN_ACT;
+                // rollout.py:244 env.limit_act(act): through ActNormWrapper the NORMALISED action is clipped to [-1, 1]
+                const R lo = cfg.act_norm ? (R)-1 : L.act_lo[i], up = cfg.act_norm ? (R)1 : L.act_up[i];
+                rec[RC::OFF_ACT + i] = act[i];
+                rec[RC::OFF_ACT_APP + i] = m_min(m_max(act[i], lo), up);
+            }
+#pragma unroll
+            for (int i = 0; i < DO; i++) {
+                rec[RC::OFF_OBS + i] = obs[i];
+                if (m_isnan(obs[i])) status |= SRE_ST_NAN_OBS;
+            }
+#pragma unroll
+            for (int i = 0; i < DS; i++) rec[RC::OFF_STATE + i] = L.s[i];
+#pragma unroll
+            for (int i = 0; i < NH; i++) rec[RC::OFF_HIDDEN + i] = L.h[i];
+            // ---- SimPyEnv.step ----
+            R rew;
+            int inside;
+            const bool done = L.step(cfg, act_env, rew, inside);
+            if (inside < 0) status |= SRE_ST_NAN_STATE;
+            E::observe(L.s, obs);
+            rec[RC::OFF_REW] = rew;
+            ret_ep += rew;
+            t_ep += 1;
+            st_steps += 1;
+            flag = done ? SRE_ROW_DONE : SRE_ROW_STEP;
+            if (done && io.stop_on_done) {
+                lane_state = CLOSING;
+                failed_ep = (inside != 1);
+            }
+        } else if (lane_state == RUN || lane_state == CLOSING) {
+            // closing row (rollout.py:309-311): final observation / state, nothing else
+            if (cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
+#pragma unroll
+            for (int i = 0; i < DO; i++) rec[RC::OFF_OBS + i] = obs[i];
+#pragma unroll
+            for (int i = 0; i < DS; i++) rec[RC::OFF_STATE + i] = L.s[i];
+#pragma unroll
+            for (int i = 0; i < NH; i++) rec[RC::OFF_HIDDEN + i] = L.h[i];
+            const bool complete = (lane_state == CLOSING);
+            flag = complete ? SRE_ROW_TERMINAL : SRE_ROW_TRUNCATED;
+            finish_episode(complete);
+            if (io.auto_reset && row < T - 1) {
+                episode += 1;
+                start_episode();
+                lane_state = RUN;
+            } else {
+                lane_state = IDLE;
+            }
+        }
+
+        if (record) {
+#pragma unroll
+            for (int i = 0; i < W; i++) stage[lane * W + i] = rec[i];
+            __syncwarp();
+            if (n_valid_lanes > 0)
+                warp_store_row<R>(stage, static_cast<R *>(io.traj) + (row * N + warp_env0) * W, n_valid_lanes * W, vec_ok,
+                                  lane);
+            __syncwarp();
+        }
+        if (io.row_flag && valid) io.row_flag[row * N + n] = flag;
+        if (!record && !io.row_flag) {
+            // early exit accounting: the warp leaves when every lane is idle
+            if (__ballot_sync(0xffffffffu, lane_state != IDLE) == 0u) break;
+        }
+    }
+    if (valid && io.status) io.status[n] = status;
+
+    // ---- statistics: warp shuffle -> one atomic set per warp ----
+    if (io.stats) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st_eps += __shfl_xor_sync(0xffffffffu, st_eps, o);
+            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
+            st_ret2 += __shfl_xor_sync(0xffffffffu, st_ret2, o);
+            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+            st_steps += __shfl_xor_sync(0xffffffffu, st_steps, o);
+            st_failed += __shfl_xor_sync(0xffffffffu, st_failed, o);
+            st_min = fmin(st_min, __shfl_xor_sync(0xffffffffu, st_min, o));
+            st_max = fmax(st_max, __shfl_xor_sync(0xffffffffu, st_max, o));
+        }
+        if (lane == 0) {
+            atomicAdd(io.stats + SRE_STAT_EPISODES, st_eps);
+            atomicAdd(io.stats + SRE_STAT_SUM_RET, st_ret);
+            atomicAdd(io.stats + SRE_STAT_SUM_RET2, st_ret2);
+            atomicAdd(io.stats + SRE_STAT_SUM_LEN, st_len);
+            atomicAdd(io.stats + SRE_STAT_STEPS, st_steps);
+            atomicAdd(io.stats + SRE_STAT_FAILED, st_failed);
+            if (st_eps > 0) {
+                atomic_min_double(io.stats + SRE_STAT_MIN_RET, st_min);
+                atomic_max_double(io.stats + SRE_STAT_MAX_RET, st_max);
+            }
+        }
+    }
+}
+
+// host-side: pick the policy variant, size shared memory, launch
+template <int KIND, typename R>
+int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const KIO &io, cudaStream_t stream);
+
+template <int KIND, typename R, int PV>
+static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPolicy &pol, const KIO &io,
+                             cudaStream_t stream) {
+    constexpr int W = Rec<KIND, R>::W;
+    const int threads = 128;
+    const long long blocks = (io.n_envs + threads - 1) / threads;
+    const size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
+    auto kern = rollout_kernel<KIND, R, PV>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<(unsigned)blocks, threads, smem, stream>>>(cfg, distr, pol, io);
+    return (int)cudaGetLastError();
+}
+
+template <int KIND, typename R>
+int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const KIO &io, cudaStream_t stream) {
+    using E = Env<KIND, R>;
+    if (pol.kind == SRE_POL_ACTIONS || pol.kind == SRE_POL_IDLE) {
+        pol.smem_floats = 0;
+        return launch_rollout_pv<KIND, R, SRE_PV_ACTIONS>(cfg, distr, pol, io, stream);
+    }
+    if (pol.kind == SRE_POL_LINEAR) {
+        pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);
+        return launch_rollout_pv<KIND, R, SRE_PV_LINEAR>(cfg, distr, pol, io, stream);
+    }
+    // FNN: the register-resident fast path needs [do, H, H, da] with tanh hidden and linear output
+    const bool two_hidden = pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
+                            pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
+                            !pol.cartpole_feats;
+    if (two_hidden && pol.sizes[1] == 64) {
+        pol.smem_floats = FnnFast<E::DO, 64, E::DA>::SMEM_FLOATS;
+        return launch_rollout_pv<KIND, R, SRE_PV_FNN64>(cfg, distr, pol, io, stream);
+    }
+    if (two_hidden && pol.sizes[1] == 32) {
+        pol.smem_floats = FnnFast<E::DO, 32, E::DA>::SMEM_FLOATS;
+        return launch_rollout_pv<KIND, R, SRE_PV_FNN32>(cfg, distr, pol, io, stream);
+    }
+    if (two_hidden && pol.sizes[1] == 16) {
+        pol.smem_floats = FnnFast<E::DO, 16, E::DA>::SMEM_FLOATS;
+        return launch_rollout_pv<KIND, R, SRE_PV_FNN16>(cfg, distr, pol, io, stream);
+    }
+    pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);
+    return launch_rollout_pv<KIND, R, SRE_PV_GENERIC>(cfg, distr, pol, io, stream);
+}
+
+}  // namespace sre
