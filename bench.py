@@ -1,0 +1,303 @@
+"""
+bench.py -- env-steps/s of the pysim rollout hot path (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload qq|qcp|qbb] [--envs M]
+
+A "step" is one pass of the hot path over one batch: ONE launch of the persistent-horizon kernel that takes
+2^20 environments per GPU through 600 simulation steps (config 2 of BASELINE.json: QQubeSwingUpSim, dt = 1/250,
+ActNormWrapper, DomainRandWrapperLive with the default qq randomizer, fused FNN [64,64] tanh policy,
+auto-reset so that every lane steps for the whole horizon).  Prints ONE JSON line (rank 0).
+
+ value      env-steps/s, whole job, inputs resident in HBM (device-timed with CUDA events, max over ranks)
+ e2e        the same through the public sampler call with HOST buffers: policy parameters copied from pinned host
+            memory every step, returns / lengths / statistics read back to the host every step
+ roofline   FP32-FMA roofline of the rollout kernel; the peak is MEASURED live with an FMA-only kernel because
+            MEASURED_PEAKS.json carries no FP32 figure
+ cpu_baseline  the CPU oracle port (oracle/sre_oracle.c, OpenMP) on a bounded sample of the same workload
+
+--impl reference times the reference's CPU implementation of the path.  The reference is Python and does not
+exist on the GPU box, so this arm runs the C restatement of it (oracle/, `kind: "port"`) on all host threads.
+"""
+import argparse
+import json
+import os
+import os.path as osp
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = osp.dirname(osp.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+QQ_NAMES = ["gravity_const", "motor_resistance", "motor_back_emf", "mass_rot_pole", "length_rot_pole",
+            "damping_rot_pole", "mass_pend_pole", "length_pend_pole", "damping_pend_pole"]
+
+# algorithmic work per env-step (FLOP convention stated there): env + fused FNN [64,64]
+FLOP_PER_STEP = {"qq": 120 + 9217, "qcp": 375 + 9089, "qbb": 260 + 2 * (8 * 16 + 16 * 16 + 16 * 2) + 34}
+RECORD_BYTES = {"qq": 53, "qcp": 53, "qbb": 93}
+
+
+def qq_randomizer(nom):
+    """create_default_randomizer_qq (domain_randomization/default_randomizers.py:376-416) as a table."""
+    div = dict(gravity_const=10, damping_rot_pole=4, damping_pend_pole=4)
+    clip = dict(gravity_const=1e-3, motor_resistance=1e-3, damping_rot_pole=1e-9, damping_pend_pole=1e-9)
+    return [dict(param_index=i, kind="normal", a=nom[i], b=nom[i] / div.get(k, 5), clip_lo=clip.get(k, 1e-4))
+            for i, k in enumerate(QQ_NAMES)]
+
+
+def fnn_weights(sizes, seed=0, scale=0.3):
+    rng = np.random.RandomState(seed)
+    return (rng.randn(sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(len(sizes) - 1))) * scale).astype(np.float32)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.p = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.25)
+        self.p.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def cpu_port_run(workload, n_envs, horizon, threads, seed=0):
+    """The oracle port on the host cores: same workload (DR + FNN [64,64] + ActNorm), bounded sample."""
+    sys.path.insert(0, osp.join(ROOT, "oracle"))
+    import oracle as O
+
+    assert workload == "qq"
+    sizes = [6, 64, 64, 1]
+    w = fnn_weights(sizes)
+    pol = O.make_policy(O.POL_FNN, w, sizes=sizes)
+    tab = O.make_distr_table(qq_randomizer(O.nominal_params(O.QQ)))
+    t0 = time.perf_counter()
+    res = O.rollout_batch(O.QQ, 1 / 250.0, horizon, n_envs, horizon, policy=pol, act_norm=True, distr=tab, seed=seed,
+                          record=False, n_threads=threads)
+    dt = time.perf_counter() - t0
+    return int(res["steps"]), dt
+
+
+def cpu_port_bounded(workload, horizon, threads, target_s=12.0):
+    steps, dt = cpu_port_run(workload, 256 * threads, horizon, threads)  # calibration
+    rate = steps / dt
+    n = int(max(256 * threads, min(1 << 20, rate * target_s / horizon)))
+    steps, dt = cpu_port_run(workload, n, horizon, threads)
+    return steps / dt, f"{n} envs x {horizon} steps (QQube + DR + FNN[64,64]) in {dt:.1f} s on {threads} threads", n
+
+
+def run_reference_arm(args):
+    """--impl reference: the CPU implementation of the path on the host cores (the oracle port; see module doc)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    horizon = 600
+    per_step_s = []
+    sample = ""
+    rate0, _, n = cpu_port_bounded(args.workload, horizon, threads, target_s=6.0)
+    for i in range(args.warmup + args.steps):
+        steps, dt = cpu_port_run(args.workload, n, horizon, threads, seed=i)
+        if i >= args.warmup:
+            per_step_s.append((steps, dt))
+    tot_steps = sum(s for s, _ in per_step_s)
+    tot_t = sum(t for _, t in per_step_s)
+    value = tot_steps / tot_t
+    sample = f"{n} envs x {horizon} steps per bench step, {threads} OpenMP threads"
+    line = dict(impl="reference", metric="env-steps/sec", value=value, unit="env-steps/s", n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=1e3 * tot_t / max(1, args.steps), higher_is_better=True, scaling="weak",
+                vs_baseline=None, dtype="f64", data="synthetic",
+                config=dict(workload="QQubeSwingUpSim dt=1/250 H=600 + ActNorm + DomainRandWrapperLive(default qq) + FNN[64,64]",
+                            envs_per_step=n, horizon=horizon),
+                cpu_baseline=dict(value=value, unit="env-steps/s", cores=threads, kind="port", sample=sample),
+                e2e=dict(value=value, unit="env-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+def measure_fma_peak(E, L, torch, dev, dtype_code):
+    """FMA-only kernel, all SMs, 32 independent chains per thread: the FP32 (or FP64) roofline denominator."""
+    import ctypes as C
+
+    sink = torch.zeros(4, dtype=torch.float32, device=dev)
+    flops = C.c_double()
+    blocks, threads, iters = 148 * 8, 256, 4096
+    best = 0.0
+    s = torch.cuda.current_stream().cuda_stream
+    for it in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        L.check(L.lib().sre_bench_fma(dtype_code, iters, blocks, threads, C.c_void_p(sink.data_ptr()), C.byref(flops),
+                                      C.c_void_p(s)), "sre_bench_fma")
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3))
+    return best / 1e12
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="qq")
+    ap.add_argument("--envs", type=int, default=1 << 20, help="environments per GPU")
+    ap.add_argument("--horizon", type=int, default=600)
+    ap.add_argument("--hidden", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import simurlacra_b200.engine as E
+    from simurlacra_b200 import _lib as L
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert args.warmup >= 3, "timing rules: at least 3 warm-up steps"
+
+    N, H, hid = args.envs, args.horizon, args.hidden
+    T = H + 1
+    sizes = [6, hid, hid, 1]
+    w_host = torch.from_numpy(fnn_weights(sizes)).pin_memory()
+    w_dev = w_host.to(dev)
+    cfg = E.make_cfg(L.QQ, 1 / 250.0, H, dtype=torch.float32, act_norm=True)
+    distr = E.make_distr_table(qq_randomizer(E.nominal_params(L.QQ)))
+    pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(i, e2e):
+        """One pass of the hot path. Device-resident variant (e2e=False) or through host buffers (e2e=True)."""
+        if e2e:
+            w_dev.copy_(w_host, non_blocking=True)  # policy update: pinned host -> device (the reference pickles
+            # the state_dict to every worker each sample(), parallel_rollout_sampler.py:269)
+        res = E.rollout(cfg, pol, N, T, device=dev, distr=distr, seed=i, env_offset=rank * N, auto_reset=True,
+                        record=False)
+        if world > 1:  # the statistics the learner logs: one small NCCL all-reduce
+            dist.all_reduce(res["stats"][:6])
+        if e2e:
+            return res["ret"].cpu(), res["length"].cpu(), res["stats"].cpu()
+        return res
+
+    # ---- device-resident timing ----
+    for i in range(args.warmup):
+        one_step(i, False)
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    ev = []
+    total_env_steps = 0.0
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)  # L2 flush between timed iterations (not timed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = one_step(args.warmup + i, False)
+        e1.record()
+        ev.append((e0, e1, res["stats"]))
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    t_dev = sum(a.elapsed_time(b) for a, b, _ in ev) * 1e-3
+    steps_dev = sum(float(s[L.STAT_STEPS]) for _, _, s in ev)  # after the all-reduce: whole job
+    if world == 1:
+        total_env_steps = steps_dev
+    else:
+        total_env_steps = steps_dev  # stats were all-reduced: already the sum over ranks
+        tt = torch.tensor([t_dev], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_dev = float(tt)
+    value = total_env_steps / t_dev
+
+    # ---- end-to-end through host buffers ----
+    for i in range(2):
+        one_step(i, True)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = 0.0
+    for i in range(args.steps):
+        ret_h, len_h, st_h = one_step(100 + i, True)
+        e2e_steps += float(st_h[L.STAT_STEPS])
+    barrier()
+    t_e2e = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_e2e = float(tt)
+    e2e_value = e2e_steps / t_e2e
+
+    if rank == 0:
+        # kernel time == step time here: the step is a single kernel launch
+        fma_peak = measure_fma_peak(E, L, torch, dev, L.F32)
+        per_rank_steps = total_env_steps / world
+        flop = FLOP_PER_STEP["qq"] if hid == 64 else 120 + 2 * (6 * hid + hid * hid + hid) + 2 * hid + 1
+        achieved = per_rank_steps * flop / t_dev / 1e12
+        line = dict(metric="env-steps/sec", value=value, unit="env-steps/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=1e3 * t_dev / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype="f32", data="synthetic",
+                    config=dict(workload=f"QQubeSwingUpSim dt=1/250 H={H} + ActNorm + DomainRandWrapperLive(default qq) + fused FNN[{hid},{hid}]",
+                                envs_per_gpu=N, horizon=H, auto_reset=True, trajectory="returns+lengths+stats",
+                                l2="flushed between timed iterations (256 MB fill)", parallelism=f"env-shard x{world}"),
+                    e2e=dict(value=e2e_value, unit="env-steps/s", h2d_bytes_per_step=int(w_host.numel() * 4),
+                             d2h_bytes_per_step=int(N * 8 + 64)),
+                    gpu_launches=args.steps,
+                    clocks=clk,
+                    roofline=dict(bound="fp32_fma", achieved=achieved, peak=fma_peak, unit="TFLOP/s", frac=achieved / fma_peak,
+                                  traffic=None, flop_per_env_step=flop,
+                                  peak_source="measured live: FMA-only kernel (sre_bench_fma), best of 4; MEASURED_PEAKS.json has no FP32 figure"))
+        if not args.no_cpu_baseline and world == 1:
+            threads = os.cpu_count() or 1
+            v, sample, _ = cpu_port_bounded("qq", H, threads)
+            line["cpu_baseline"] = dict(value=v, unit="env-steps/s", cores=threads, kind="port", sample=sample)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

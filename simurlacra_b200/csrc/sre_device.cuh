@@ -1,6 +1,6 @@
 // sre_device.cuh -- device-side building blocks shared by all kernels: math wrappers templated on the real
 // type (float = production build, double = verification build), Philox4x32-10 and the sample mappings of the
-// engine's RNG specification (restated independently in oracle/sre_oracle.c, pinned by the Random123 vectors).
+// engine's RNG specification (restated independently by the CPU checker under oracle/, pinned by the Random123 vectors).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>

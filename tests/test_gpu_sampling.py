@@ -1,0 +1,135 @@
+"""
+GPU tests of the sampling semantics: shard invariance (the analogue of Pyrado/tests/test_sampling.py:594-646,
+same rollouts for any worker count), auto-reset (min_steps) sampling, stop_on_done=False, ragged batch sizes,
+fp32 vs fp64 builds on the full-size batch through size-independent properties.
+"""
+import numpy as np
+import pytest
+import torch
+
+from test_gpu_engine import DEV, _t, default_distr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def E():
+    import simurlacra_b200.engine as eng
+
+    return eng
+
+
+def _fnn(E, d, hid, seed=0, scale=0.5):
+    from simurlacra_b200 import _lib as L
+
+    rng = np.random.RandomState(seed)
+    sizes = [d["do"], hid, hid, d["da"]]
+    w = (rng.randn(sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(3))) * scale).astype(np.float32)
+    return E.make_policy(L.POL_FNN, _t(w, torch.float32), sizes=sizes), w, sizes
+
+
+@pytest.mark.parametrize("n_envs", [1, 31, 33, 130, 1000])
+def test_ragged_batches_and_shard_invariance(E, n_envs):
+    """Any split of the global env range gives bit-identical rollouts (Philox keys use the global index), for
+    batch sizes that are not multiples of the warp / vector width."""
+    from simurlacra_b200 import _lib as L
+
+    d = E.dims(L.QQ)
+    cfg = E.make_cfg(L.QQ, 1 / 250.0, 60, dtype=torch.float32, act_norm=True)
+    pol, _, _ = _fnn(E, d, 32)
+    distr = E.make_distr_table(default_distr("qq-su"))
+    full = E.rollout(cfg, pol, n_envs, 61, device=DEV, distr=distr, seed=3)
+    cut = n_envs // 3
+    parts = [E.rollout(cfg, pol, cut, 61, device=DEV, distr=distr, seed=3),
+             E.rollout(cfg, pol, n_envs - cut, 61, device=DEV, distr=distr, seed=3, env_offset=cut)] if cut else []
+    if parts:
+        for k in ("ret", "length", "params"):
+            assert torch.equal(full[k], torch.cat([p[k] for p in parts]))
+        assert torch.equal(full["traj"], torch.cat([p["traj"] for p in parts], dim=1))
+        assert torch.equal(full["row_flag"], torch.cat([p["row_flag"] for p in parts], dim=1))
+    if n_envs > 1:
+        assert len(torch.unique(full["ret"])) == n_envs  # rollouts within one batch differ
+    # the same call twice is deterministic
+    again = E.rollout(cfg, pol, n_envs, 61, device=DEV, distr=distr, seed=3)
+    assert torch.equal(full["traj"], again["traj"])
+
+
+def test_auto_reset_rows_are_consistent_episodes(E, orc):
+    """min_steps-style sampling: every lane fills its row budget with consecutive episodes (episode index
+    e, e+1, ...), each closed by a TERMINAL row; the pieces equal single-episode rollouts of the oracle."""
+    from simurlacra_b200 import _lib as L
+
+    kind = L.BOB  # ball-on-beam episodes end early (ball leaves the beam), so lanes see several episodes
+    d = E.dims(kind)
+    N, T = 64, 400
+    cfg = E.make_cfg(kind, 0.01, 500, dtype=torch.float64)
+    pol = E.make_policy(L.POL_IDLE)
+    res = E.rollout(cfg, pol, N, T, device=DEV, seed=9, auto_reset=True)
+    flags = res["row_flag"].cpu().numpy()
+    st, rw = res["state"].cpu().numpy(), res["rew"].cpu().numpy()
+    n_eps, n_steps = 0, 0
+    for n in range(N):
+        rows = flags[:, n]
+        assert rows[-1] in (L.ROW_TERMINAL, L.ROW_TRUNCATED)
+        start, ep = 0, 0
+        for r in range(T):
+            if rows[r] >= L.ROW_TERMINAL:
+                length = r - start
+                if rows[r] == L.ROW_TERMINAL:
+                    assert rows[r - 1] == L.ROW_DONE
+                    ref = orc.rollout_batch(kind, 0.01, 500, 1, 500, policy=orc.make_policy(orc.POL_IDLE), seed=9,
+                                            env_offset=n, episode=ep)
+                    assert int(ref["length"][0]) == length
+                    assert np.abs(st[start: r + 1, n] - ref["state"][: length + 1, 0]).max() < 1e-9
+                    np.testing.assert_allclose(rw[start:r, n], ref["rew"][:length, 0], rtol=1e-9, atol=1e-12)
+                    n_eps += 1
+                n_steps += length
+                start, ep = r + 1, ep + 1
+        assert ep >= 2
+    stats = res["stats"].cpu().numpy()
+    assert stats[L.STAT_EPISODES] == n_eps and stats[L.STAT_STEPS] == n_steps
+    assert stats[L.STAT_FAILED] == n_eps  # every complete ball-on-beam episode here ended by leaving the state space
+
+
+def test_stop_on_done_false_keeps_stepping(E, orc):
+    from simurlacra_b200 import _lib as L
+
+    kind = L.OMO
+    cfg = E.make_cfg(kind, 0.02, 40, dtype=torch.float64)
+    N, H = 32, 100
+    rng = np.random.RandomState(0)
+    acts = rng.uniform(-40, 40, size=(H, N, 1))
+    res = E.rollout(cfg, E.make_policy(L.POL_ACTIONS), N, H + 1, device=DEV, actions=_t(acts, torch.float64), seed=1,
+                    stop_on_done=False)
+    ref = orc.rollout_batch(kind, 0.02, 40, N, H, policy=orc.make_policy(orc.POL_ACTIONS), actions=acts, seed=1,
+                            stop_on_done=False)
+    flags = res["row_flag"].cpu().numpy()
+    np.testing.assert_array_equal(flags[:H] == L.ROW_DONE, ref["done"].astype(bool))
+    assert (flags[H] == L.ROW_TRUNCATED).all()
+    assert np.abs(res["state"].cpu().numpy() - ref["state"]).max() < 1e-9
+    np.testing.assert_allclose(res["rew"][:H].cpu().numpy(), ref["rew"], rtol=1e-9, atol=1e-9)
+
+
+def test_full_size_fp32_properties(E):
+    """BASELINE config 2 at full size (2^20 envs, 600 steps, DR, fused FNN [64,64]) through size-independent
+    properties: every lane takes exactly n_rows - 1 - episodes steps in auto-reset mode, statistics add up, no NaN
+    status, determinism of the checksum across two launches, and a random subset equals its own re-run as a shard."""
+    from simurlacra_b200 import _lib as L
+
+    d = E.dims(L.QQ)
+    N, T = 1 << 20, 601
+    cfg = E.make_cfg(L.QQ, 1 / 250.0, 600, dtype=torch.float32, act_norm=True)
+    pol, _, _ = _fnn(E, d, 64, scale=0.3)
+    distr = E.make_distr_table(default_distr("qq-su"))
+    a = E.rollout(cfg, pol, N, T, device=DEV, distr=distr, seed=0, auto_reset=True, record=False)
+    b = E.rollout(cfg, pol, N, T, device=DEV, distr=distr, seed=0, auto_reset=True, record=False)
+    sa, sb = a["stats"].cpu().numpy(), b["stats"].cpu().numpy()
+    assert sa[L.STAT_STEPS] == sb[L.STAT_STEPS] and sa[L.STAT_EPISODES] == sb[L.STAT_EPISODES]
+    assert torch.equal(a["ret"], b["ret"]) and torch.equal(a["length"], b["length"])
+    assert int(a["status"].abs().sum()) == 0
+    assert torch.isfinite(a["ret"]).all()
+    # each complete episode costs one closing row; lanes never idle in auto-reset mode
+    assert sa[L.STAT_STEPS] <= N * (T - 1) and sa[L.STAT_STEPS] >= N * (T - 1) - sa[L.STAT_EPISODES] - N
+    lo = 12345
+    sub = E.rollout(cfg, pol, 4096, T, device=DEV, distr=distr, seed=0, env_offset=lo, auto_reset=True, record=False)
+    assert torch.equal(sub["ret"], a["ret"][lo: lo + 4096]) and torch.equal(sub["length"], a["length"][lo: lo + 4096])
