@@ -20,6 +20,31 @@ template <typename R> __global__ void __launch_bounds__(256) fma_kernel(long lon
     if (s == (R)123.456) sink[0] = s;  // keeps the loop alive, never true in practice
 }
 
+// packed FP32 (Blackwell fma.rn.f32x2): 16 independent 64-bit accumulator pairs = the same 32 FMA chains per thread
+__global__ void __launch_bounds__(256) fma2_kernel(long long iters, float seed, float *sink) {
+    unsigned long long acc[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        float lo = seed + (float)(threadIdx.x + 2 * i), hi = lo + 1.f;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(acc[i]) : "f"(lo), "f"(hi));
+    }
+    unsigned long long a, b;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(a) : "f"(1.0000001f));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(b) : "f"(1e-7f));
+    for (long long it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(acc[i]) : "l"(a), "l"(b));
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc[i]));
+        s += lo + hi;
+    }
+    if (s == 123.456f) sink[0] = s;
+}
+
 __global__ void __launch_bounds__(256) hbm_write_kernel(float4 *dst, long long n_vec) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const float4 v = make_float4(1.f, 2.f, 3.f, 4.f);
@@ -33,9 +58,10 @@ using namespace sre;
 extern "C" {
 
 int sre_bench_fma(int dtype, int64_t iters, int blocks, int threads, float *sink, double *flops, void *stream) {
-    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64, SRE_E_DTYPE, "unknown dtype %d", dtype);
+    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64 || dtype == 2, SRE_E_DTYPE, "unknown dtype %d", dtype);
     SRE_CHECK_ARG(iters > 0 && blocks > 0 && threads > 0 && threads <= 256 && sink, SRE_E_ARG, "bad launch shape");
-    if (dtype == SRE_F32) fma_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
+    if (dtype == 2) fma2_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
+    else if (dtype == SRE_F32) fma_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
     else fma_kernel<double><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5, reinterpret_cast<double *>(sink));
     if (flops) *flops = 2.0 * 32.0 * (double)iters * (double)blocks * (double)threads;
     SRE_CUDA(cudaGetLastError());
