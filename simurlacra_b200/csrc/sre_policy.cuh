@@ -26,102 +26,179 @@ SRE_DEV float nonlin_f(int kind, float x) {
     return x;
 }
 
-// ---- shared-memory layout -----------------------------------------------------------------------------
-// Generic path: the torch layout unchanged.
-// Fast path FnnFast<IN,HID,OUT>: every layer transposed to [in][out] so that four consecutive OUTPUT neurons of
-// one input are a single 128-bit broadcast load:  W1T[IN][HID] | b1[HID] | W2T[HID][HID] | b2[HID] | W3[OUT][HID] | b3[OUT]
-template <int IN, int HID, int OUT> struct FnnFast {
-    static constexpr int OFF_W1T = 0;
-    static constexpr int OFF_B1 = OFF_W1T + IN * HID;
-    static constexpr int OFF_W2T = OFF_B1 + HID;
-    static constexpr int OFF_B2 = OFF_W2T + HID * HID;
-    static constexpr int OFF_W3 = OFF_B2 + HID;
-    static constexpr int OFF_B3 = OFF_W3 + OUT * HID;
-    static constexpr int SMEM_FLOATS = ((OFF_B3 + OUT + 3) / 4) * 4;
-    static constexpr int N_WEIGHTS = IN * HID + HID + HID * HID + HID + OUT * HID + OUT;
-    static constexpr int JC = 8;  // output neurons of layer 2 accumulated together (independent FMA chains)
+// ---- warp-tiled FNN [IN, HID, HID, OUT], tanh hidden, linear output -------------------------------------------
+// The dominant cost of a rollout step is layer 2 (HID x HID MACs per env).  A thread-per-env dot product needs one
+// warp-broadcast shared-memory load per 4 FMAs and a broadcast load only delivers 8 bytes per shared-memory
+// wavefront (measured: profiles/r01_a_*), which caps the kernel well below the FMA roofline.  Here a warp treats
+// its 32 environments as a [32 x HID] x [HID x HID] product with an 8 x (HID/8) register tile per lane:
+//   lane = (r, c), r = lane / 8 owns environments 8r .. 8r+7, c = lane % 8 owns outputs {16m + 2c, 16m + 2c + 1}
+//   per k: 2 x LDS.128 of activations (h1s[k][env], written once per step by the owner lanes)
+//          HID/16 x LDS.128 of weights stored DUPLICATED {w, w} so that they feed packed FP32 FMAs directly
+//          4 x (HID/8) FFMA2 (Blackwell fma.rn.f32x2: two environments per instruction, one issue slot)
+// Layer 1 (IN <= 8 inputs) and the dynamics stay thread-per-env; layer 3 is folded into the epilogue of layer 2
+// and reduced across the 8 lanes of a row group with a transpose-reduce (7 shuffles), which leaves the action of
+// environment e on lane e.
+SRE_DEV unsigned long long pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+SRE_DEV void unpack2(unsigned long long v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+SRE_DEV unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
 
-    // all threads of the CTA cooperate; caller syncs afterwards
+// tanh(x) = sign(x) * (1 - t) / (1 + t), t = 2^(-2 log2(e) |x|): two MUFU ops (ex2, rcp), absolute error < 3e-7
+SRE_DEV float tanh_fast(float x) {
+    const float ax = fabsf(x);
+    float t, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(ax * -2.8853900817779268f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + t));
+    return copysignf((1.0f - t) * r, x);
+}
+
+template <int IN, int HID, int OUT, bool FAST_TANH> struct FnnTiled {
+    static constexpr int TN = HID / 8;  // outputs per lane
+    static constexpr int NM = TN / 2;   // 16-output chunks
+    static_assert(HID % 16 == 0 && HID <= 64, "hidden width must be 16, 32 or 64");
+    // block-shared weights (floats)
+    static constexpr int OFF_W1T = 0;                      // [IN][HID]
+    static constexpr int OFF_B1 = OFF_W1T + IN * HID;      // [HID]
+    static constexpr int OFF_W2D = OFF_B1 + HID;           // [HID k][HID j][2] duplicated
+    static constexpr int OFF_B2 = OFF_W2D + 2 * HID * HID; // [HID]
+    static constexpr int OFF_W3D = OFF_B2 + HID;           // [OUT][HID][2] duplicated
+    static constexpr int OFF_B3 = OFF_W3D + 2 * OUT * HID; // [OUT]
+    static constexpr int W_FLOATS = ((OFF_B3 + OUT + 3) / 4) * 4;
+    static constexpr int H1S_FLOATS = HID * 32;            // per warp: h1s[k][env]
+    static constexpr int WARPS = 4;
+    static constexpr int SMEM_FLOATS = W_FLOATS + WARPS * H1S_FLOATS;
+
+    SRE_DEV static float act(float x) { return FAST_TANH ? tanh_fast(x) : tanhf(x); }
+
     SRE_DEV static void stage(const float *__restrict__ w, float *sm) {
         const float *W1 = w, *b1 = W1 + IN * HID, *W2 = b1 + HID, *b2 = W2 + HID * HID, *W3 = b2 + HID,
                     *b3 = W3 + OUT * HID;
-        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) {
-            const int j = i / IN, k = i % IN;  // W1[j][k]
-            sm[OFF_W1T + k * HID + j] = W1[i];
-        }
+        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) sm[OFF_W1T + (i % IN) * HID + i / IN] = W1[i];
         for (int i = threadIdx.x; i < HID * HID; i += blockDim.x) {
             const int j = i / HID, k = i % HID;  // W2[j][k]
-            sm[OFF_W2T + k * HID + j] = W2[i];
+            sm[OFF_W2D + 2 * (k * HID + j)] = W2[i];
+            sm[OFF_W2D + 2 * (k * HID + j) + 1] = W2[i];
         }
         for (int i = threadIdx.x; i < HID; i += blockDim.x) { sm[OFF_B1 + i] = b1[i]; sm[OFF_B2 + i] = b2[i]; }
-        for (int i = threadIdx.x; i < OUT * HID; i += blockDim.x) sm[OFF_W3 + i] = W3[i];
+        for (int i = threadIdx.x; i < OUT * HID; i += blockDim.x) { sm[OFF_W3D + 2 * i] = W3[i]; sm[OFF_W3D + 2 * i + 1] = W3[i]; }
         for (int i = threadIdx.x; i < OUT; i += blockDim.x) sm[OFF_B3 + i] = b3[i];
     }
 
-    // tanh hidden layers, linear output
-    SRE_DEV static void forward(const float *sm, const float *x, float *out) {
-        float h1[HID];
-        const float4 *b1v = reinterpret_cast<const float4 *>(sm + OFF_B1);
-#pragma unroll
-        for (int j = 0; j < HID / 4; j++) {
-            const float4 b = b1v[j];
-            h1[4 * j] = b.x; h1[4 * j + 1] = b.y; h1[4 * j + 2] = b.z; h1[4 * j + 3] = b.w;
-        }
-#pragma unroll
-        for (int i = 0; i < IN; i++) {
-            const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W1T + i * HID);
-#pragma unroll
-            for (int j = 0; j < HID / 4; j++) {
-                const float4 w = wv[j];
-                h1[4 * j] = fmaf(w.x, x[i], h1[4 * j]);
-                h1[4 * j + 1] = fmaf(w.y, x[i], h1[4 * j + 1]);
-                h1[4 * j + 2] = fmaf(w.z, x[i], h1[4 * j + 2]);
-                h1[4 * j + 3] = fmaf(w.w, x[i], h1[4 * j + 3]);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < HID; j++) h1[j] = tanhf(h1[j]);
-#pragma unroll
-        for (int o = 0; o < OUT; o++) out[o] = sm[OFF_B3 + o];
-        // layers 2 and 3 fused: h2[j] is consumed by the output layer as soon as its dot product is complete
+    // Warp-cooperative: every lane of the warp must call this (convergent), x = observation of the lane's own env.
+    SRE_DEV static void forward(const float *sm, float *h1s, const float *x, float *out, int lane) {
+        // ---- layer 1, thread-per-env, 16 outputs at a time -> h1s[j][lane] ----
+        __syncwarp();  // previous step's readers are done with h1s
 #pragma unroll 1
-        for (int j0 = 0; j0 < HID; j0 += JC) {
-            float acc[JC];
-            {
-                const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B2 + j0);
+        for (int j0 = 0; j0 < HID; j0 += 16) {
+            float a[16];
+            const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B1 + j0);
 #pragma unroll
-                for (int q = 0; q < JC / 4; q++) {
-                    const float4 b = bv[q];
-                    acc[4 * q] = b.x; acc[4 * q + 1] = b.y; acc[4 * q + 2] = b.z; acc[4 * q + 3] = b.w;
-                }
+            for (int q = 0; q < 4; q++) {
+                const float4 b = bv[q];
+                a[4 * q] = b.x; a[4 * q + 1] = b.y; a[4 * q + 2] = b.z; a[4 * q + 3] = b.w;
             }
-            const float *w2 = sm + OFF_W2T + j0;
 #pragma unroll
-            for (int k = 0; k < HID; k++) {
-                const float4 *wv = reinterpret_cast<const float4 *>(w2 + k * HID);
+            for (int i = 0; i < IN; i++) {
+                const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W1T + i * HID + j0);
 #pragma unroll
-                for (int q = 0; q < JC / 4; q++) {
+                for (int q = 0; q < 4; q++) {
                     const float4 w = wv[q];
-                    acc[4 * q] = fmaf(w.x, h1[k], acc[4 * q]);
-                    acc[4 * q + 1] = fmaf(w.y, h1[k], acc[4 * q + 1]);
-                    acc[4 * q + 2] = fmaf(w.z, h1[k], acc[4 * q + 2]);
-                    acc[4 * q + 3] = fmaf(w.w, h1[k], acc[4 * q + 3]);
+                    a[4 * q] = fmaf(w.x, x[i], a[4 * q]);
+                    a[4 * q + 1] = fmaf(w.y, x[i], a[4 * q + 1]);
+                    a[4 * q + 2] = fmaf(w.z, x[i], a[4 * q + 2]);
+                    a[4 * q + 3] = fmaf(w.w, x[i], a[4 * q + 3]);
                 }
             }
 #pragma unroll
-            for (int jj = 0; jj < JC; jj++) acc[jj] = tanhf(acc[jj]);
+            for (int q = 0; q < 16; q++) h1s[(j0 + q) * 32 + lane] = act(a[q]);
+        }
+        __syncwarp();
+        // ---- layer 2, 8 envs x TN outputs per lane, packed over environment pairs ----
+        const int r = lane >> 3, c = lane & 7;
+        unsigned long long acc[4][TN];
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+            const float2 b = *reinterpret_cast<const float2 *>(sm + OFF_B2 + 16 * m + 2 * c);
+#pragma unroll
+            for (int ip = 0; ip < 4; ip++) {
+                acc[ip][2 * m] = pack2(b.x, b.x);
+                acc[ip][2 * m + 1] = pack2(b.y, b.y);
+            }
+        }
+        const float *ap = h1s + 8 * r;
+        const float *wp = sm + OFF_W2D + 4 * c;
+#pragma unroll 8
+        for (int k = 0; k < HID; k++) {
+            const ulonglong2 a01 = *reinterpret_cast<const ulonglong2 *>(ap + k * 32);
+            const ulonglong2 a23 = *reinterpret_cast<const ulonglong2 *>(ap + k * 32 + 4);
+            const unsigned long long a[4] = {a01.x, a01.y, a23.x, a23.y};
+#pragma unroll
+            for (int m = 0; m < NM; m++) {
+                const ulonglong2 w = *reinterpret_cast<const ulonglong2 *>(wp + 2 * (k * HID + 16 * m));
+#pragma unroll
+                for (int ip = 0; ip < 4; ip++) {
+                    acc[ip][2 * m] = fma2(a[ip], w.x, acc[ip][2 * m]);
+                    acc[ip][2 * m + 1] = fma2(a[ip], w.y, acc[ip][2 * m + 1]);
+                }
+            }
+        }
+        // ---- epilogue: tanh, layer 3 partial sums over this lane's TN outputs ----
+        unsigned long long part[OUT][4];
+#pragma unroll
+        for (int o = 0; o < OUT; o++)
+#pragma unroll
+            for (int ip = 0; ip < 4; ip++) part[o][ip] = 0ull;
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+#pragma unroll
+            for (int ip = 0; ip < 4; ip++) {
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    float lo, hi;
+                    unpack2(acc[ip][2 * m + h], lo, hi);
+                    acc[ip][2 * m + h] = pack2(act(lo), act(hi));
+                }
+            }
 #pragma unroll
             for (int o = 0; o < OUT; o++) {
-                const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W3 + o * HID + j0);
+                const ulonglong2 w3 = *reinterpret_cast<const ulonglong2 *>(sm + OFF_W3D + 2 * (o * HID + 16 * m + 2 * c));
 #pragma unroll
-                for (int q = 0; q < JC / 4; q++) {
-                    const float4 w = wv[q];
-                    out[o] = fmaf(w.x, acc[4 * q], out[o]);
-                    out[o] = fmaf(w.y, acc[4 * q + 1], out[o]);
-                    out[o] = fmaf(w.z, acc[4 * q + 2], out[o]);
-                    out[o] = fmaf(w.w, acc[4 * q + 3], out[o]);
+                for (int ip = 0; ip < 4; ip++) {
+                    part[o][ip] = fma2(acc[ip][2 * m], w3.x, part[o][ip]);
+                    part[o][ip] = fma2(acc[ip][2 * m + 1], w3.y, part[o][ip]);
                 }
             }
+        }
+        // ---- transpose-reduce over the 8 lanes of the row group: lane (r, c) ends with env 8r + c ----
+#pragma unroll
+        for (int o = 0; o < OUT; o++) {
+            float v[8];
+#pragma unroll
+            for (int ip = 0; ip < 4; ip++) unpack2(part[o][ip], v[2 * ip], v[2 * ip + 1]);
+            float u[4];
+            const bool b4 = c & 4;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float send = b4 ? v[i] : v[4 + i], keep = b4 ? v[4 + i] : v[i];
+                u[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            float t[2];
+            const bool b2 = c & 2;
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const float send = b2 ? u[i] : u[2 + i], keep = b2 ? u[2 + i] : u[i];
+                t[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            const bool b1 = c & 1;
+            const float send = b1 ? t[0] : t[1], keep = b1 ? t[1] : t[0];
+            out[o] = sm[OFF_B3 + o] + (keep + __shfl_xor_sync(0xffffffffu, send, 1));
         }
     }
 };

@@ -86,12 +86,14 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     using E = Env<KIND, R>;
     using RC = Rec<KIND, R>;
     constexpr int DS = E::DS, DO = E::DO, DA = E::DA, DP = E::DP, NH = E::NH, W = RC::W;
-    using Fast = FnnFast<DO, (PV >= 16 ? PV : 16), DA>;
+    // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
+    using Fast = FnnTiled<DO, (PV >= 16 ? PV : 16), DA, sizeof(R) == 4>;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *sm_w = reinterpret_cast<float *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
+    float *h1s = sm_w + Fast::W_FLOATS + warp * Fast::H1S_FLOATS;  // only meaningful for the tiled FNN variants
 
     if (PV >= 16) Fast::stage(pol.weights, sm_w);
     else if (PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) stage_generic(pol, sm_w);
@@ -111,6 +113,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     Lane<KIND, R> L;
     R dp[DP];
     R obs[DO];
+#pragma unroll
+    for (int i = 0; i < DO; i++) obs[i] = (R)0;
     uint32_t episode = io.episode;
     int lane_state = valid ? RUN : IDLE;
     int t_ep = 0;
@@ -180,26 +184,28 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         for (int i = 0; i < W; i++) rec[i] = (R)0;
         unsigned char flag = SRE_ROW_IDLE;
 
-        if (lane_state == RUN && row < T - 1) {
-            if (cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
-            // ---- policy (float32) ----
-            R act[DA];
-            if (PV == SRE_PV_ACTIONS) {
+        const bool stepping = (lane_state == RUN && row < T - 1);
+        const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
+        if ((stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
+        // ---- policy (float32).  The tiled FNN is warp-cooperative, so it runs outside the per-lane branches ----
+        R act[DA];
+        if (PV == SRE_PV_ACTIONS) {
 #pragma unroll
-                for (int i = 0; i < DA; i++)
-                    act[i] = (io.actions && !io.idle_policy)
-                                 ? static_cast<const R *>(io.actions)[(row * N + n) * DA + i]
-                                 : (R)0;
-            } else {
-                float of[DO], af[DA];
+            for (int i = 0; i < DA; i++)
+                act[i] = (stepping && io.actions && !io.idle_policy)
+                             ? static_cast<const R *>(io.actions)[(row * N + n) * DA + i]
+                             : (R)0;
+        } else {
+            float of[DO], af[DA];
 #pragma unroll
-                for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
-                if (PV >= 16) Fast::forward(sm_w, of, af);
-                else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
-                else linear_forward<DO, DA>(pol, sm_w, of, af);
+            for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
+            if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
+            else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
+            else linear_forward<DO, DA>(pol, sm_w, of, af);
 #pragma unroll
-                for (int i = 0; i < DA; i++) act[i] = (R)af[i];
-            }
+            for (int i = 0; i < DA; i++) act[i] = (R)af[i];
+        }
+        if (stepping) {
             // ---- wrappers: ActNormWrapper._process_act (action_normalization.py:69-75) ----
             R act_env[DA];
 #pragma unroll
@@ -235,9 +241,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 lane_state = CLOSING;
                 failed_ep = (inside != 1);
             }
-        } else if (lane_state == RUN || lane_state == CLOSING) {
+        } else if (closing) {
             // closing row (rollout.py:309-311): final observation / state, nothing else
-            if (cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
 #pragma unroll
             for (int i = 0; i < DO; i++) rec[RC::OFF_OBS + i] = obs[i];
 #pragma unroll
@@ -335,15 +340,15 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
     if (two_hidden && pol.sizes[1] == 64) {
-        pol.smem_floats = FnnFast<E::DO, 64, E::DA>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 64, E::DA, true>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN64>(cfg, distr, pol, io, stream);
     }
     if (two_hidden && pol.sizes[1] == 32) {
-        pol.smem_floats = FnnFast<E::DO, 32, E::DA>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 32, E::DA, true>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN32>(cfg, distr, pol, io, stream);
     }
     if (two_hidden && pol.sizes[1] == 16) {
-        pol.smem_floats = FnnFast<E::DO, 16, E::DA>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 16, E::DA, true>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN16>(cfg, distr, pol, io, stream);
     }
     pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);

@@ -48,7 +48,8 @@ def test_ragged_batches_and_shard_invariance(E, n_envs):
         assert torch.equal(full["traj"], torch.cat([p["traj"] for p in parts], dim=1))
         assert torch.equal(full["row_flag"], torch.cat([p["row_flag"] for p in parts], dim=1))
     if n_envs > 1:
-        assert len(torch.unique(full["ret"])) == n_envs  # rollouts within one batch differ
+        # rollouts within one batch differ (float32 returns may collide by chance for a handful)
+        assert len(torch.unique(full["ret"])) >= 0.99 * n_envs and len(torch.unique(full["params"], dim=0)) == n_envs
     # the same call twice is deterministic
     again = E.rollout(cfg, pol, n_envs, 61, device=DEV, distr=distr, seed=3)
     assert torch.equal(full["traj"], again["traj"])
