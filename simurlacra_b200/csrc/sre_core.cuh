@@ -121,8 +121,12 @@ template <int KIND, typename R> struct Lane {
     R c_max;
     R s[E::DS];
     R h[E::NH > 0 ? E::NH : 1];
+    R trig[2];  // sin / cos the dynamics share with the observation of the current state (QQ: al, QCP: th)
     int curr_step;
     int yielded_final;
+
+    // Env.observe (environments/base.py:203 and the overrides); also refreshes `trig`
+    SRE_DEV void observe(R *obs) { E::observe(s, obs, trig); }
 
     // domain_param setter: _calc_constants + _create_spaces + task.reset (base.py:112-124)
     SRE_DEV void set_params(const KCfg<R> &cfg, const R *dp) {
@@ -175,7 +179,7 @@ template <int KIND, typename R> struct Lane {
         R a[E::DA];
 #pragma unroll
         for (int i = 0; i < E::DA; i++) a[i] = m_min(m_max(act[i], act_lo[i]), act_up[i]);  // limit_act, box.py:180
-        E::step(c, cfg.dt, cfg.flags, s, h, a);
+        E::step(c, cfg.dt, cfg.flags, s, h, a, trig);  // trig belongs to the pre-step state
         curr_step += 1;
         inside = contains();
         bool done = (inside != 1);  // never_succeeded: done == has_failed (tasks/base.py:159-172)

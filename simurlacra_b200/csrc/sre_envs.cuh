@@ -49,12 +49,12 @@ template <typename R> struct Env<SRE_QQ, R> {
     }
     // _dyn :89-125 evaluated once; the fork's pseudo-RK4 (:127-146) evaluates _dyn at self.state on every stage,
     // so the update is exactly v += dt*a0, p += dt*v0 + dt^2/2*a0.
-    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act) {
+    // trig = (sin al, cos al) of the CURRENT state, produced by observe(): the dynamics reuse it
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
         R u = act[0];
         if (c.thold_neg <= u && u <= c.thold_pos) u = (R)0;
         const R thd = s[2], ald = s[3];
-        R sa, ca;
-        m_sincos(s[1], sa, ca);
+        const R sa = trig[0], ca = trig[1];
         const R s2a = (R)2 * sa * ca;  // sin(2 al)
         const R a = c.c0 + c.c1 * (sa * sa);
         const R b = c.c2 * ca;
@@ -71,11 +71,13 @@ template <typename R> struct Env<SRE_QQ, R> {
         s[2] += dt * thdd;
         s[3] += dt * aldd;
     }
-    SRE_DEV static void observe(const R *s, R *obs) {  // :148-149
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) {  // :148-149
         m_sincos(s[0], obs[0], obs[1]);
         m_sincos(s[1], obs[2], obs[3]);
         obs[4] = s[2];
         obs[5] = s[3];
+        trig[0] = obs[2];
+        trig[1] = obs[3];
     }
     SRE_DEV static void reset_hidden(const R *dp, int flags, const R *s, R *h) {}
     SRE_DEV static void state_from_init(const R *init, int n_cols, R *s) {
@@ -135,6 +137,9 @@ template <typename R> struct Env<SRE_QCP, R> {
     SRE_DEV static void accel(const Consts &c, int flags, R th, R xd, R thd, R u, R thdd_in, R &xdd, R &thdd) {
         R sn, cs;
         m_sincos(th, sn, cs);
+        accel_sc(c, flags, sn, cs, xd, thd, u, thdd_in, xdd, thdd);
+    }
+    SRE_DEV static void accel_sc(const Consts &c, int flags, R sn, R cs, R xd, R thd, R u, R thdd_in, R &xdd, R &thdd) {
         const bool simple = flags & SRE_F_SIMPLE_DYN;
         if (!simple && c.thold_neg <= u && u <= c.thold_pos) u = (R)0;
         R f_tot = c.k_u * u - c.k_xd * xd;
@@ -154,11 +159,12 @@ template <typename R> struct Env<SRE_QCP, R> {
     }
     // rk4() :591-655 over [0, dt] on [x, th, xd, thd, u] with derivative [xd + xdd dt, thd + thdd dt, xdd, thdd, 0];
     // th_ddot of stage i feeds stage i+1, the mean of the four becomes the next step's carry (:652).
-    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act) {
+    // trig = (sin th, cos th) of the current state (from observe()), used by the first RK4 stage
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
         const R u = act[0];
         const R dt2 = dt * (R)0.5;
         R a1x, a1t, a2x, a2t, a3x, a3t, a4x, a4t;
-        accel(c, flags, s[1], s[2], s[3], u, h[0], a1x, a1t);
+        accel_sc(c, flags, trig[0], trig[1], s[2], s[3], u, h[0], a1x, a1t);
         const R k1x = s[2] + a1x * dt, k1t = s[3] + a1t * dt;
         accel(c, flags, s[1] + dt2 * k1t, s[2] + dt2 * a1x, s[3] + dt2 * a1t, u, a1t, a2x, a2t);
         const R k2x = (s[2] + dt2 * a1x) + a2x * dt, k2t = (s[3] + dt2 * a1t) + a2t * dt;
@@ -173,11 +179,13 @@ template <typename R> struct Env<SRE_QCP, R> {
         s[3] += w * (a1t + (R)2 * a2t + (R)2 * a3t + a4t);
         h[0] = (a1t + a2t + a3t + a4t) / (R)4;
     }
-    SRE_DEV static void observe(const R *s, R *obs) {  // :108-109
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) {  // :108-109
         obs[0] = s[0];
         m_sincos(s[1], obs[1], obs[2]);
         obs[3] = s[2];
         obs[4] = s[3];
+        trig[0] = obs[1];
+        trig[1] = obs[2];
     }
     SRE_DEV static void reset_hidden(const R *dp, int flags, const R *s, R *h) { h[0] = (R)0; }  // :101-106
     SRE_DEV static void state_from_init(const R *init, int n_cols, R *s) {
@@ -238,7 +246,7 @@ template <typename R> struct Env<SRE_QBB, R> {
         act_lo[0] = act_lo[1] = (R)-3; act_up[0] = act_up[1] = (R)3;  // MAX_ACT_QBB
     }
     // _step_dynamics :247-331
-    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act) {
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
         const bool simple = flags & SRE_F_SIMPLE_DYN;
         if (!simple && c.Vxn <= act[0] && act[0] <= c.Vxp) act[0] = (R)0;  // dead zones :261-264 (in place)
         if (!simple && c.Vyn <= act[1] && act[1] <= c.Vyp) act[1] = (R)0;
@@ -275,7 +283,7 @@ template <typename R> struct Env<SRE_QBB, R> {
 #pragma unroll
         for (int i = 0; i < 4; i++) s[i] += s[4 + i] * dt;
     }
-    SRE_DEV static void observe(const R *s, R *obs) {
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) {
 #pragma unroll
         for (int i = 0; i < 8; i++) obs[i] = s[i];
     }
@@ -364,7 +372,7 @@ template <typename R> struct Env<SRE_BOB, R> {
         act_lo[0] = (R)(-max_act); act_up[0] = (R)max_act;
     }
     // _step_dynamics :110-130
-    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act) {
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
         const R x = s[0], xd = s[2], ad = s[3];
         R sa, ca;
         m_sincos(s[1] + c.ang_offset, sa, ca);
@@ -374,7 +382,7 @@ template <typename R> struct Env<SRE_BOB, R> {
         s[2] += xdd * dt; s[3] += add * dt;
         s[0] += s[2] * dt; s[1] += s[3] * dt;
     }
-    SRE_DEV static void observe(const R *s, R *obs) {
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) {
 #pragma unroll
         for (int i = 0; i < 4; i++) obs[i] = s[i];
     }
@@ -413,13 +421,13 @@ template <typename R> struct Env<SRE_OMO, R> {
         act_lo[0] = (R)(-k); act_up[0] = (R)k;
     }
     // _step_dynamics :105-116: forward Euler on s' = A s + B a
-    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act) {
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
         const R sd0 = s[1];
         const R sd1 = c.A10 * s[0] + c.A11 * s[1] + c.B1 * act[0];
         s[0] += sd0 * dt;
         s[1] += sd1 * dt;
     }
-    SRE_DEV static void observe(const R *s, R *obs) { obs[0] = s[0]; obs[1] = s[1]; }
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) { obs[0] = s[0]; obs[1] = s[1]; }
     SRE_DEV static void reset_hidden(const R *dp, int flags, const R *s, R *h) {}
     SRE_DEV static void state_from_init(const R *init, int n_cols, R *s) { s[0] = init[0]; s[1] = init[1]; }
     SRE_DEV static void init_box(const R *dp, int wild_init, bool right, double *lo, double *up) {  // :57-58

@@ -50,13 +50,15 @@ SRE_DEV unsigned long long fma2(unsigned long long a, unsigned long long b, unsi
     return d;
 }
 
-// tanh(x) = sign(x) * (1 - t) / (1 + t), t = 2^(-2 log2(e) |x|): two MUFU ops (ex2, rcp), absolute error < 3e-7
-SRE_DEV float tanh_fast(float x) {
-    const float ax = fabsf(x);
+// tanh(z) = 1 - 2 / (1 + e^(2z)).  The caller passes zs = 2 log2(e) z (the scale is folded into the weights and
+// biases of the producing layer when they are staged), so this is MUFU.EX2, FADD, MUFU.RCP, FFMA: four
+// instructions, absolute error < 3e-7; saturates correctly (ex2 -> inf gives rcp -> 0, ex2 -> 0 gives -1).
+#define SRE_TANH_PRESCALE 2.8853900817779268f
+SRE_DEV float tanh_prescaled(float zs) {
     float t, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(ax * -2.8853900817779268f));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(zs));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + t));
-    return copysignf((1.0f - t) * r, x);
+    return fmaf(-2.0f, r, 1.0f);
 }
 
 template <int IN, int HID, int OUT, bool FAST_TANH> struct FnnTiled {
@@ -72,21 +74,22 @@ template <int IN, int HID, int OUT, bool FAST_TANH> struct FnnTiled {
     static constexpr int OFF_B3 = OFF_W3D + 2 * OUT * HID; // [OUT]
     static constexpr int W_FLOATS = ((OFF_B3 + OUT + 3) / 4) * 4;
     static constexpr int H1S_FLOATS = HID * 32;            // per warp: h1s[k][env]
-    static constexpr int WARPS = 4;
+    static constexpr int WARPS = FAST_TANH ? 8 : 4;        // production build: 256-thread CTAs, 2 per SM
     static constexpr int SMEM_FLOATS = W_FLOATS + WARPS * H1S_FLOATS;
+    static constexpr float PRE = FAST_TANH ? SRE_TANH_PRESCALE : 1.0f;  // folded into W1, b1, W2, b2
 
-    SRE_DEV static float act(float x) { return FAST_TANH ? tanh_fast(x) : tanhf(x); }
+    SRE_DEV static float act(float x) { return FAST_TANH ? tanh_prescaled(x) : tanhf(x); }
 
     SRE_DEV static void stage(const float *__restrict__ w, float *sm) {
         const float *W1 = w, *b1 = W1 + IN * HID, *W2 = b1 + HID, *b2 = W2 + HID * HID, *W3 = b2 + HID,
                     *b3 = W3 + OUT * HID;
-        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) sm[OFF_W1T + (i % IN) * HID + i / IN] = W1[i];
+        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) sm[OFF_W1T + (i % IN) * HID + i / IN] = PRE * W1[i];
         for (int i = threadIdx.x; i < HID * HID; i += blockDim.x) {
             const int j = i / HID, k = i % HID;  // W2[j][k]
-            sm[OFF_W2D + 2 * (k * HID + j)] = W2[i];
-            sm[OFF_W2D + 2 * (k * HID + j) + 1] = W2[i];
+            sm[OFF_W2D + 2 * (k * HID + j)] = PRE * W2[i];
+            sm[OFF_W2D + 2 * (k * HID + j) + 1] = PRE * W2[i];
         }
-        for (int i = threadIdx.x; i < HID; i += blockDim.x) { sm[OFF_B1 + i] = b1[i]; sm[OFF_B2 + i] = b2[i]; }
+        for (int i = threadIdx.x; i < HID; i += blockDim.x) { sm[OFF_B1 + i] = PRE * b1[i]; sm[OFF_B2 + i] = PRE * b2[i]; }
         for (int i = threadIdx.x; i < OUT * HID; i += blockDim.x) { sm[OFF_W3D + 2 * i] = W3[i]; sm[OFF_W3D + 2 * i + 1] = W3[i]; }
         for (int i = threadIdx.x; i < OUT; i += blockDim.x) sm[OFF_B3 + i] = b3[i];
     }

@@ -79,8 +79,14 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
     } while (assumed != old);
 }
 
+// CTA shape per variant: the tiled FNN production build runs 256-thread CTAs, two per SM (16 warps, 128 registers)
+template <typename R, int PV> struct LaunchShape {
+    static constexpr int THREADS = (PV >= 16 && sizeof(R) == 4) ? 256 : 128;
+    static constexpr int MIN_BLOCKS = (PV >= 16 && sizeof(R) == 4) ? 2 : 1;
+};
+
 template <int KIND, typename R, int PV>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__((LaunchShape<R, PV>::THREADS), (LaunchShape<R, PV>::MIN_BLOCKS))
 rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDistr distr,
                const __grid_constant__ KPolicy pol, const __grid_constant__ KIO io) {
     using E = Env<KIND, R>;
@@ -122,9 +128,12 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     bool first_episode = true;
     bool failed_ep = false;
     int status = 0;
-    // statistics over completed episodes of this lane
-    double st_eps = 0, st_ret = 0, st_ret2 = 0, st_len = 0, st_steps = 0, st_failed = 0;
-    double st_min = 1e300, st_max = -1e300;
+    // statistics: accumulated per CTA in shared memory when an episode closes (rare), so that no statistics
+    // registers stay live across the hot loop; one global atomic set per CTA at the end
+    __shared__ double sm_stats[SRE_N_STATS];
+    if (threadIdx.x < SRE_N_STATS)
+        sm_stats[threadIdx.x] = threadIdx.x == SRE_STAT_MIN_RET ? 1e300 : (threadIdx.x == SRE_STAT_MAX_RET ? -1e300 : 0.0);
+    __syncthreads();
 
     auto start_episode = [&]() {
 #pragma unroll
@@ -154,7 +163,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             sample_init<KIND, R>(cfg, dp, io.seed, genv, episode, init);
         }
         L.reset(cfg, dp, init, n_cols);
-        E::observe(L.s, obs);
+        L.observe(obs);
         t_ep = 0;
         ret_ep = (R)0;
         failed_ep = false;
@@ -165,14 +174,17 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             if (io.length) io.length[n] = t_ep;
             first_episode = false;
         }
-        if (complete) {
-            st_eps += 1;
-            st_ret += (double)ret_ep;
-            st_ret2 += (double)ret_ep * (double)ret_ep;
-            st_len += t_ep;
-            st_failed += failed_ep ? 1 : 0;
-            st_min = fmin(st_min, (double)ret_ep);
-            st_max = fmax(st_max, (double)ret_ep);
+        if (io.stats) {
+            atomicAdd(&sm_stats[SRE_STAT_STEPS], (double)t_ep);
+            if (complete) {
+                atomicAdd(&sm_stats[SRE_STAT_EPISODES], 1.0);
+                atomicAdd(&sm_stats[SRE_STAT_SUM_RET], (double)ret_ep);
+                atomicAdd(&sm_stats[SRE_STAT_SUM_RET2], (double)ret_ep * (double)ret_ep);
+                atomicAdd(&sm_stats[SRE_STAT_SUM_LEN], (double)t_ep);
+                if (failed_ep) atomicAdd(&sm_stats[SRE_STAT_FAILED], 1.0);
+                atomic_min_double(&sm_stats[SRE_STAT_MIN_RET], (double)ret_ep);
+                atomic_max_double(&sm_stats[SRE_STAT_MAX_RET], (double)ret_ep);
+            }
         }
     };
 
@@ -231,11 +243,10 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             int inside;
             const bool done = L.step(cfg, act_env, rew, inside);
             if (inside < 0) status |= SRE_ST_NAN_STATE;
-            E::observe(L.s, obs);
+            L.observe(obs);
             rec[RC::OFF_REW] = rew;
             ret_ep += rew;
             t_ep += 1;
-            st_steps += 1;
             flag = done ? SRE_ROW_DONE : SRE_ROW_STEP;
             if (done && io.stop_on_done) {
                 lane_state = CLOSING;
@@ -278,30 +289,15 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     }
     if (valid && io.status) io.status[n] = status;
 
-    // ---- statistics: warp shuffle -> one atomic set per warp ----
+    // ---- statistics: one atomic set per CTA ----
     if (io.stats) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st_eps += __shfl_xor_sync(0xffffffffu, st_eps, o);
-            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
-            st_ret2 += __shfl_xor_sync(0xffffffffu, st_ret2, o);
-            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
-            st_steps += __shfl_xor_sync(0xffffffffu, st_steps, o);
-            st_failed += __shfl_xor_sync(0xffffffffu, st_failed, o);
-            st_min = fmin(st_min, __shfl_xor_sync(0xffffffffu, st_min, o));
-            st_max = fmax(st_max, __shfl_xor_sync(0xffffffffu, st_max, o));
-        }
-        if (lane == 0) {
-            atomicAdd(io.stats + SRE_STAT_EPISODES, st_eps);
-            atomicAdd(io.stats + SRE_STAT_SUM_RET, st_ret);
-            atomicAdd(io.stats + SRE_STAT_SUM_RET2, st_ret2);
-            atomicAdd(io.stats + SRE_STAT_SUM_LEN, st_len);
-            atomicAdd(io.stats + SRE_STAT_STEPS, st_steps);
-            atomicAdd(io.stats + SRE_STAT_FAILED, st_failed);
-            if (st_eps > 0) {
-                atomic_min_double(io.stats + SRE_STAT_MIN_RET, st_min);
-                atomic_max_double(io.stats + SRE_STAT_MAX_RET, st_max);
-            }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            if (sm_stats[threadIdx.x] != 0.0) atomicAdd(io.stats + threadIdx.x, sm_stats[threadIdx.x]);
+        } else if (threadIdx.x == SRE_STAT_MIN_RET) {
+            if (sm_stats[SRE_STAT_EPISODES] > 0) atomic_min_double(io.stats + SRE_STAT_MIN_RET, sm_stats[SRE_STAT_MIN_RET]);
+        } else if (threadIdx.x == SRE_STAT_MAX_RET) {
+            if (sm_stats[SRE_STAT_EPISODES] > 0) atomic_max_double(io.stats + SRE_STAT_MAX_RET, sm_stats[SRE_STAT_MAX_RET]);
         }
     }
 }
@@ -314,7 +310,7 @@ template <int KIND, typename R, int PV>
 static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPolicy &pol, const KIO &io,
                              cudaStream_t stream) {
     constexpr int W = Rec<KIND, R>::W;
-    const int threads = 128;
+    const int threads = LaunchShape<R, PV>::THREADS;
     const long long blocks = (io.n_envs + threads - 1) / threads;
     const size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
     auto kern = rollout_kernel<KIND, R, PV>;
@@ -340,15 +336,15 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
     if (two_hidden && pol.sizes[1] == 64) {
-        pol.smem_floats = FnnTiled<E::DO, 64, E::DA, true>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 64, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN64>(cfg, distr, pol, io, stream);
     }
     if (two_hidden && pol.sizes[1] == 32) {
-        pol.smem_floats = FnnTiled<E::DO, 32, E::DA, true>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 32, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN32>(cfg, distr, pol, io, stream);
     }
     if (two_hidden && pol.sizes[1] == 16) {
-        pol.smem_floats = FnnTiled<E::DO, 16, E::DA, true>::SMEM_FLOATS;
+        pol.smem_floats = FnnTiled<E::DO, 16, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN16>(cfg, distr, pol, io, stream);
     }
     pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);

@@ -78,7 +78,7 @@ __global__ void reset_kernel(const __grid_constant__ KCfg<R> cfg, const R *param
     curr_step[n] = 0;
     if (obs) {
         R o[E::DO];
-        E::observe(L.s, o);
+        L.observe(o);
         if (cfg.obs_noise) add_obs_noise<E::DO, R>(cfg, seed, env_offset + (unsigned long long)n, episode, 0u, o);
 #pragma unroll
         for (int i = 0; i < E::DO; i++) obs[n * E::DO + i] = o[i];
@@ -114,6 +114,8 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     }
     R r;
     int inside;
+    R o[E::DO];
+    L.observe(o);  // refreshes the trig terms of the loaded state
     const bool d = L.step(cfg, a, r, inside);
     if (inside < 0) st |= SRE_ST_NAN_STATE;
 #pragma unroll
@@ -121,8 +123,7 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
 #pragma unroll
     for (int i = 0; i < E::NH; i++) hidden[n * NHS + i] = L.h[i];
     curr_step[n] = L.curr_step;
-    R o[E::DO];
-    E::observe(L.s, o);
+    L.observe(o);
     if (cfg.obs_noise)
         add_obs_noise<E::DO, R>(cfg, seed, env_offset + (unsigned long long)n, episode, (uint32_t)L.curr_step, o);
 #pragma unroll
@@ -136,10 +137,10 @@ template <int KIND, typename R> __global__ void observe_kernel(const R *state, R
     using E = Env<KIND, R>;
     const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
-    R s[E::DS], o[E::DO];
+    R s[E::DS], o[E::DO], trig[2];
 #pragma unroll
     for (int i = 0; i < E::DS; i++) s[i] = state[n * E::DS + i];
-    E::observe(s, o);
+    E::observe(s, o, trig);
 #pragma unroll
     for (int i = 0; i < E::DO; i++) obs[n * E::DO + i] = o[i];
 }
