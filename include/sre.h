@@ -250,6 +250,14 @@ int sre_step(const sre_env_cfg *cfg, const void *params, const void *act, void *
              uint64_t env_offset, uint32_t episode, int64_t n, void *stream);
 /* Env.observe (environments/base.py:203 and the overrides): obs [N, do] from state [N, ds] */
 int sre_observe(const sre_env_cfg *cfg, const void *state, void *obs, int64_t n, void *stream);
+/* Task.step_rew (tasks/base.py:108, tasks/desired_state.py:107,146) for a batch: state [N, ds], act [N, da]
+ * (UNCLIPPED, inner-env units) -> rew [N]; params as in sre_derive (c_max of ScaledExp depends on them) */
+int sre_step_rew(const sre_env_cfg *cfg, const void *params, const void *state, const void *act, void *rew, int64_t n,
+                 void *stream);
+/* The same for a free-standing task without an env (Task / RewFcn objects, tasks/reward_functions.py:202-297):
+ * task->Q is row-major [ds, ds], task->R [da, da]; c_max only matters for SRE_REW_SCALED_EXP */
+int sre_task_step_rew(const sre_task *task, int dtype, int ds, int da, double c_max, const void *state,
+                      const void *act, void *rew, int64_t n, void *stream);
 /* Policy.forward for a batch: obs float [N, n_obs] -> act float [N, n_act] (always float32) */
 int sre_policy_forward(const sre_policy *pol, const float *obs, int n_obs, float *act, int n_act, int64_t n,
                        void *stream);

@@ -137,6 +137,8 @@ SIGNATURES = {
     "sre_reset": (_I, [C.POINTER(EnvCfg), _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _U64, _U64, _U32, _I64, _VP]),
     "sre_step": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _U64, _U64, _U32, _I64, _VP]),
     "sre_observe": (_I, [C.POINTER(EnvCfg), _VP, _VP, _I64, _VP]),
+    "sre_step_rew": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _I64, _VP]),
+    "sre_task_step_rew": (_I, [C.POINTER(Task), _I, _I, _I, _D, _VP, _VP, _VP, _I64, _VP]),
     "sre_policy_forward": (_I, [C.POINTER(Policy), _VP, _I, _VP, _I, _I64, _VP]),
     "sre_rollout": (_I, [C.POINTER(EnvCfg), C.POINTER(Policy), C.POINTER(RolloutIO), _VP]),
     "sre_last_launch_count": (_I, []),

@@ -99,7 +99,9 @@ int reset_dispatch(const sre_env_cfg *, const void *, const void *, int, const u
 int step_dispatch(const sre_env_cfg *, const void *, const void *, void *, void *, int *, void *, void *,
                   unsigned char *, int *, unsigned long long, unsigned long long, unsigned, long long, cudaStream_t);
 int observe_dispatch(const sre_env_cfg *, const void *, void *, long long, cudaStream_t);
+int step_rew_dispatch(const sre_env_cfg *, const void *, const void *, const void *, void *, long long, cudaStream_t);
 int policy_forward_dispatch(const KPolicy &, const float *, int, float *, int, long long, cudaStream_t);
+int task_rew_dispatch(const sre_task *, int, int, int, double, const void *, const void *, void *, long long, cudaStream_t);
 
 static int cuda_ret(int e, const char *what) {
     if (e != 0) set_error("%s: %s", what, cudaGetErrorString((cudaError_t)e));
@@ -300,6 +302,26 @@ int sre_observe(const sre_env_cfg *cfg, const void *state, void *obs, int64_t n,
     SRE_CHECK_ARG(state && obs && n >= 0, SRE_E_ARG, "NULL pointer or n < 0");
     if (n == 0) return 0;
     return cuda_ret(observe_dispatch(cfg, state, obs, n, (cudaStream_t)stream), "sre_observe");
+}
+
+int sre_step_rew(const sre_env_cfg *cfg, const void *params, const void *state, const void *act, void *rew, int64_t n,
+                 void *stream) {
+    int e = check_cfg(cfg);
+    if (e) return e;
+    SRE_CHECK_ARG(state && act && rew && n >= 0, SRE_E_ARG, "NULL pointer or n < 0");
+    if (n == 0) return 0;
+    return cuda_ret(step_rew_dispatch(cfg, params, state, act, rew, n, (cudaStream_t)stream), "sre_step_rew");
+}
+
+int sre_task_step_rew(const sre_task *task, int dtype, int ds, int da, double c_max, const void *state,
+                      const void *act, void *rew, int64_t n, void *stream) {
+    SRE_CHECK_ARG(task && state && act && rew && n >= 0, SRE_E_ARG, "NULL pointer or n < 0");
+    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64, SRE_E_DTYPE, "unknown dtype %d", dtype);
+    SRE_CHECK_ARG(ds >= 1 && ds <= SRE_MAX_DS && da >= 1 && da <= SRE_MAX_DA, SRE_E_ARG, "ds %d / da %d out of range", ds, da);
+    SRE_CHECK_ARG(task->rew_kind >= 0 && task->rew_kind <= 2, SRE_E_ARG, "unknown reward kind %d", task->rew_kind);
+    if (n == 0) return 0;
+    return cuda_ret(task_rew_dispatch(task, dtype, ds, da, c_max, state, act, rew, n, (cudaStream_t)stream),
+                    "sre_task_step_rew");
 }
 
 int sre_policy_forward(const sre_policy *pol, const float *obs, int n_obs, float *act, int n_act, int64_t n,

@@ -5,6 +5,8 @@
 
 namespace sre {
 
+static inline unsigned nblocks(long long n, int t) { return (unsigned)((n + t - 1) / t); }
+
 template <int KIND, typename R>
 __global__ void derive_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, long long N, R *st_lo, R *st_up,
                               R *act_lo, R *act_up, R *c_max) {
@@ -145,6 +147,80 @@ template <int KIND, typename R> __global__ void observe_kernel(const R *state, R
     for (int i = 0; i < E::DO; i++) obs[n * E::DO + i] = o[i];
 }
 
+// Task.step_rew for a batch of (state, action) pairs (tasks/desired_state.py:107-155, tasks/reward_functions.py)
+template <int KIND, typename R>
+__global__ void step_rew_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, const R *state, const R *act,
+                                R *rew, long long N) {
+    using E = Env<KIND, R>;
+    const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    R dp[E::DP];
+#pragma unroll
+    for (int i = 0; i < E::DP; i++) dp[i] = params ? params[n * E::DP + i] : cfg.base_params[i];
+    Lane<KIND, R> L;
+    L.set_params(cfg, dp);
+    R s[E::DS], a[E::DA];
+#pragma unroll
+    for (int i = 0; i < E::DS; i++) s[i] = state[n * E::DS + i];
+#pragma unroll
+    for (int i = 0; i < E::DA; i++) a[i] = act[n * E::DA + i];
+    rew[n] = step_rew<E::DS, E::DA, R>(cfg.task, s, a, L.c_max);
+}
+
+// Task.step_rew for a free-standing task (no env): runtime dims, same arithmetic as step_rew<DS, DA, R>
+template <typename R>
+__global__ void task_rew_kernel(const __grid_constant__ KTask<R> tk, int ds, int da, R c_max, const R *state,
+                                const R *act, R *rew, long long N) {
+    const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    R err[SRE_MAX_DS], a[SRE_MAX_DA];
+    for (int i = 0; i < ds; i++) err[i] = tk.state_des[i] - state[n * ds + i];
+    for (int i = 0; i < da; i++) a[i] = act[n * da + i];
+    if (tk.radial_mask) {
+        const R pi = (R)SRE_PI, two_pi = (R)(2 * SRE_PI);
+        for (int i = 0; i < ds; i++)
+            if (tk.radial_mask & (1u << i)) err[i] = m_fmod(err[i], tk.radial_mod[i]);
+        for (int i = 0; i < ds; i++) {
+            if (err[i] > pi) err[i] = two_pi - err[i];
+            if (err[i] < -pi) err[i] = -two_pi - err[i];
+        }
+    }
+    R cost = (R)0;
+    for (int i = 0; i < ds; i++) {
+        R t = (R)0;
+        for (int j = 0; j < ds; j++) t += tk.Q[i * ds + j] * err[j];
+        cost += err[i] * t;
+    }
+    for (int i = 0; i < da; i++) {
+        R t = (R)0;
+        for (int j = 0; j < da; j++) t += tk.Rm[i * da + j] * a[j];
+        cost += a[i] * t;
+    }
+    rew[n] = tk.rew_kind == SRE_REW_QUADR ? -cost : (tk.rew_kind == SRE_REW_EXP ? m_exp(-cost) : m_exp(-c_max * cost));
+}
+
+template <typename R>
+static int task_rew_t(const sre_task *task, int ds, int da, double c_max, const void *state, const void *act, void *rew,
+                      long long n, cudaStream_t s) {
+    KTask<R> k;
+    memset(&k, 0, sizeof k);
+    for (int i = 0; i < ds; i++) {
+        k.state_des[i] = (R)task->state_des[i];
+        k.radial_mod[i] = (R)task->radial_mod[i];
+        for (int j = 0; j < ds; j++) k.Q[i * ds + j] = (R)task->Q[i * ds + j];
+    }
+    for (int i = 0; i < da * da; i++) k.Rm[i] = (R)task->R[i];
+    k.rew_kind = task->rew_kind;
+    k.radial_mask = task->radial_mask;
+    task_rew_kernel<R><<<nblocks(n, 128), 128, 0, s>>>(k, ds, da, (R)c_max, (const R *)state, (const R *)act, (R *)rew, n);
+    return (int)cudaGetLastError();
+}
+int task_rew_dispatch(const sre_task *task, int dtype, int ds, int da, double c_max, const void *state, const void *act,
+                      void *rew, long long n, cudaStream_t s) {
+    return dtype == SRE_F64 ? task_rew_t<double>(task, ds, da, c_max, state, act, rew, n, s)
+                            : task_rew_t<float>(task, ds, da, c_max, state, act, rew, n, s);
+}
+
 // Policy.forward for a batch (float32): weights read from global memory through the read-only path; this is
 // the step-granular entry, the rollout kernel has its own register-resident fast path.
 __global__ void policy_forward_kernel(const __grid_constant__ KPolicy pol, const float *obs, int n_obs, float *act,
@@ -170,7 +246,6 @@ __global__ void policy_forward_kernel(const __grid_constant__ KPolicy pol, const
     default: { constexpr int K = SRE_OMO; BODY } break;                   \
     }
 
-static inline unsigned nblocks(long long n, int t) { return (unsigned)((n + t - 1) / t); }
 
 template <typename R>
 static int derive_t(const sre_env_cfg *cfg, const void *params, long long n, void *st_lo, void *st_up, void *act_lo,
@@ -260,6 +335,21 @@ static int observe_t(const sre_env_cfg *cfg, const void *state, void *obs, long 
 }
 int observe_dispatch(const sre_env_cfg *cfg, const void *state, void *obs, long long n, cudaStream_t s) {
     return cfg->dtype == SRE_F64 ? observe_t<double>(cfg, state, obs, n, s) : observe_t<float>(cfg, state, obs, n, s);
+}
+
+template <typename R>
+static int step_rew_t(const sre_env_cfg *cfg, const void *params, const void *state, const void *act, void *rew,
+                      long long n, cudaStream_t s) {
+    KCfg<R> k;
+    make_kcfg<R>(*cfg, k);
+    SRE_DISPATCH_KIND(cfg->kind, R, (step_rew_kernel<K, R><<<nblocks(n, 128), 128, 0, s>>>(
+                                        k, (const R *)params, (const R *)state, (const R *)act, (R *)rew, n));)
+    return (int)cudaGetLastError();
+}
+int step_rew_dispatch(const sre_env_cfg *cfg, const void *params, const void *state, const void *act, void *rew,
+                      long long n, cudaStream_t s) {
+    return cfg->dtype == SRE_F64 ? step_rew_t<double>(cfg, params, state, act, rew, n, s)
+                                 : step_rew_t<float>(cfg, params, state, act, rew, n, s);
 }
 
 int policy_forward_dispatch(const KPolicy &kp, const float *obs, int n_obs, float *act, int n_act, long long n,

@@ -221,6 +221,24 @@ def observe(cfg, state: torch.Tensor) -> torch.Tensor:
     return obs
 
 
+def step_rew(cfg, params, state: torch.Tensor, act: torch.Tensor) -> torch.Tensor:
+    dt_ = cfg_dtype(cfg)
+    rew = torch.empty(state.shape[0], dtype=dt_, device=state.device)
+    L.check(L.lib().sre_step_rew(C.byref(cfg), _ptr(_chk(params, dt_, "params")), _ptr(_chk(state, dt_, "state")),
+                                 _ptr(_chk(act, dt_, "act")), _ptr(rew), state.shape[0], _stream()), "sre_step_rew")
+    return rew
+
+
+def task_step_rew(task: L.Task, ds: int, da: int, c_max: float, state: torch.Tensor, act: torch.Tensor) -> torch.Tensor:
+    """Reward of a free-standing task for a batch: state [N, ds], act [N, da] (same dtype, float32 or float64)."""
+    dt_ = state.dtype
+    rew = torch.empty(state.shape[0], dtype=dt_, device=state.device)
+    L.check(L.lib().sre_task_step_rew(C.byref(task), L.F64 if dt_ == torch.float64 else L.F32, ds, da, float(c_max),
+                                      _ptr(_chk(state, dt_, "state")), _ptr(_chk(act, dt_, "act")), _ptr(rew), state.shape[0],
+                                      _stream()), "sre_task_step_rew")
+    return rew
+
+
 def policy_forward(pol: L.Policy, obs: torch.Tensor, n_act: int) -> torch.Tensor:
     _chk(obs, torch.float32, "obs")
     act = torch.empty(obs.shape[0], n_act, dtype=torch.float32, device=obs.device)

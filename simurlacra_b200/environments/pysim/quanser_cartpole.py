@@ -1,0 +1,98 @@
+"""QCartPoleSwingUpSim -- Quanser cart-pole (pyrado/environments/pysim/quanser_cartpole.py:54-588), including the
+fork's differentiable `step_diff_state` (:257-358) whose backward pass is the hand-written adjoint kernel."""
+from typing import Optional
+
+import numpy as np
+import torch
+
+import simurlacra_b200 as pyrado
+
+from ... import _lib as L
+from ... import engine as E
+from ...spaces.box import BoxSpace
+from ...tasks.desired_state import RadiallySymmDesStateTask
+from ...tasks.reward_functions import ExpQuadrErrRewFcn
+from .base import SimPyEnv
+
+MAX_ACT_QCP = 6.0  # [V]
+
+
+class QCartPoleSwingUpSim(SimPyEnv):
+    name: str = "qcp-su"
+    kind = L.QCP
+    _param_names = ("gravity_const", "cart_mass", "rail_length", "motor_efficiency", "gear_efficiency", "gear_ratio",
+                    "motor_inertia", "pinion_radius", "motor_resistance", "motor_back_emf", "pole_damping",
+                    "combined_damping", "pole_mass", "pole_length", "cart_friction_coeff", "voltage_thold_neg",
+                    "voltage_thold_pos")
+
+    def __init__(self, dt: float, max_steps: int = pyrado.inf, task_args: Optional[dict] = None, long: bool = False,
+                 simple_dynamics: bool = False, wild_init: str = "True", mass=None, **kwargs):
+        """
+        :param long: long (0.641 m) or short pole
+        :param simple_dynamics: Quanser's simplified dynamics (no Coulomb friction, no dead zone)
+        :param wild_init: the fork compares STRINGS: 'True' -> wide init box, 'False' -> narrow one, anything else
+                          (including the bool True that sac_wgrad passes) -> the third box (quanser_cartpole.py:552-560)
+        """
+        self._long, self._mass = long, mass
+        self._wild_init_arg = wild_init
+        self._x_buffer = 0.15
+        super().__init__(dt, max_steps, task_args, **kwargs)
+        self._flags = L.F_SIMPLE_DYN if simple_dynamics else 0
+        self._wild_init = 0 if wild_init == "True" else (1 if wild_init == "False" else 2)
+        self.domain_param = self.get_nominal_domain_param(long=long, mass=mass)
+
+    @classmethod
+    def get_nominal_domain_param(cls, long: bool = False, mass=None) -> dict:  # :111-143
+        m_pole, l_pole = (0.23, 0.641 / 2) if long else (0.127, 0.3365 / 2)
+        if mass is not None:
+            m_pole = mass
+        return dict(gravity_const=9.81, cart_mass=0.58, rail_length=0.814, motor_efficiency=0.9, gear_efficiency=0.9,
+                    gear_ratio=3.71, motor_inertia=3.9e-7, pinion_radius=6.35e-3, motor_resistance=2.6,
+                    motor_back_emf=7.67e-3, pole_damping=0.0024, combined_damping=5.4, pole_mass=m_pole,
+                    pole_length=l_pole, cart_friction_coeff=0.02, voltage_thold_neg=0.0, voltage_thold_pos=0.0)
+
+    def _create_spaces(self):  # :88-95, :541-560
+        l_rail = self._domain_param["rail_length"]
+        max_obs = np.array([l_rail / 2.0, 1.0, 1.0, np.inf, np.inf])
+        self._obs_space = BoxSpace(-max_obs, max_obs, labels=["x", "sin_theta", "cos_theta", "x_dot", "theta_dot"])
+        self._act_space = BoxSpace(-MAX_ACT_QCP, MAX_ACT_QCP, shape=(1,), labels=["V"])
+        max_state = np.array([l_rail / 2.0 - self._x_buffer, 4 * np.pi, 1 * l_rail, 20 * np.pi])
+        w = getattr(self, "_wild_init_arg", "True")
+        if w == "True":
+            mi = np.array([0.25, np.pi, 0.8, np.pi])
+        elif w == "False":
+            mi = np.array([0.02, 2 / 180.0 * np.pi, 0.0, 1 / 180.0 * np.pi])
+        else:
+            mi = np.array([0.02, np.pi, 0.0, 1 / 180.0 * np.pi])
+        self._state_space = BoxSpace(-max_state, max_state, labels=["x", "theta", "x_dot", "theta_dot"])
+        if not self._custom_init_space:
+            self._init_space = BoxSpace(-mi, mi, labels=["x", "theta", "x_dot", "theta_dot"])
+
+    def _create_task(self, task_args: dict):  # :573-588
+        state_des = task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0]))
+        Q = task_args.get("Q", np.diag([3e-1, 5e-1, 5e-3, 1e-3]))
+        R = task_args.get("R", np.diag([1e-3]))
+        return RadiallySymmDesStateTask(self.spec, state_des, ExpQuadrErrRewFcn(Q, R), idcs=[1])
+
+    # ---- differentiable step (quanser_cartpole.py:257-280): torch in, torch out, autograd through the adjoint kernel
+    def step_diff_state(self, state: torch.Tensor, act: torch.Tensor, act_diff: torch.Tensor = None, th_ddot=None):
+        """state [B, 4], act [B, 1] in volts (wrappers de-normalise before), th_ddot [B] carry or None.
+        Returns next_state [B, 4], rew [B], done [B] (bool), {'th_ddot': [B]}; differentiable w.r.t. state, act,
+        act_diff and th_ddot."""
+        from ...sampling.diff import QcpDiffStep
+
+        if act_diff is None:
+            act_diff = torch.zeros_like(act)
+        a_un = (act + act_diff).reshape(-1)
+        if th_ddot is None:
+            th_ddot = torch.zeros(state.shape[0], dtype=state.dtype, device=state.device)
+        cfg = E.make_cfg(self.kind, self._dt, self._max_steps, dtype=state.dtype,
+                         simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init,
+                         task=self._task_struct(), base_params=self.base_param_vector())
+        ns, rew, done, thdd = QcpDiffStep.apply(cfg, self._params, state, a_un, th_ddot.reshape(-1))
+        return ns, rew, done, {"th_ddot": thdd}
+
+    def _task_struct(self):
+        t = L.Task()
+        self._task.fill(t)
+        return t
