@@ -1,0 +1,12 @@
+"""Environment wrappers (pyrado/environment_wrappers); ActNorm and Gaussian observation noise fuse into the kernels."""
+from .action_normalization import ActNormWrapper, ObsActCatWrapper, dclamp  # noqa: F401
+from .base import EnvWrapper, EnvWrapperAct, EnvWrapperObs  # noqa: F401
+from .domain_randomization import (  # noqa: F401
+    DomainRandWrapper,
+    DomainRandWrapperBuffer,
+    DomainRandWrapperLive,
+    MetaDomainRandWrapper,
+    remove_all_dr_wrappers,
+)
+from .observation_noise import GaussianObsNoiseWrapper  # noqa: F401
+from .utils import all_envs, attr_env, attr_env_get, inner_env, insert_env_before, remove_env, typed_env  # noqa: F401

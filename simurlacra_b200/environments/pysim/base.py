@@ -173,6 +173,22 @@ class SimPyEnv(SimEnv):
             raise pyrado.ShapeErr(given=params, expected_match=(self.num_envs, self._dims["dp"]))
         self._params = params.to(self._dtype).contiguous()
 
+    def randomize_params(self, randomizer, episode: Optional[int] = None, seed: Optional[int] = None):
+        """Engine extension: draw a fresh parameter set per env from `randomizer` with one launch of the Philox
+        sampler (DomainRandomizer.randomize + domain_param setter for the whole batch).  Keyed (seed, env_offset + i,
+        episode), the key the rollout kernel uses when it samples the same randomizer in-flight."""
+        if self._params is None:
+            base = torch.as_tensor(self.base_param_vector(), dtype=self._dtype)
+            self._params = base.repeat(self.num_envs, 1).to(self.device).contiguous()
+        episode = self._episode + 1 if episode is None else episode  # the reset that follows advances to it
+        E.sample_params(self._make_cfg(), randomizer.table(self._param_names), self._params,
+                        pyrado.device_seed() if seed is None else seed, self.env_offset, episode)
+        first = self._params[0].double().cpu().numpy()
+        for i, k in enumerate(self._param_names):
+            self._domain_param[k] = float(first[i])
+        self._create_spaces()
+        self._task.reset(env_spec=self.spec)
+
     def base_param_vector(self) -> np.ndarray:
         return np.array([self._domain_param[k] for k in self._param_names], dtype=np.float64)
 
@@ -284,6 +300,12 @@ class SimPyEnv(SimEnv):
 
     def step(self, act) -> tuple:
         return self._step_impl(act, None)
+
+    def _reset_chain(self, init_state, domain_param, fusion):  # entry points of the wrapper chain
+        return self._reset_impl(init_state, domain_param, fusion)
+
+    def _step_chain(self, act, fusion) -> tuple:
+        return self._step_impl(act, fusion)
 
     def _step_impl(self, act, fusion: Optional[Fusion]) -> tuple:
         if self._state is None:

@@ -89,7 +89,10 @@ class QCartPoleSwingUpSim(SimPyEnv):
         cfg = E.make_cfg(self.kind, self._dt, self._max_steps, dtype=state.dtype,
                          simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init,
                          task=self._task_struct(), base_params=self.base_param_vector())
-        ns, rew, done, thdd = QcpDiffStep.apply(cfg, self._params, state, a_un, th_ddot.reshape(-1))
+        params = self._params if self._params is not None and self._params.shape[0] == state.shape[0] else None
+        if params is not None and params.dtype != state.dtype:
+            params = params.to(state.dtype)
+        ns, rew, done, thdd = QcpDiffStep.apply(cfg, params, state, a_un, th_ddot.reshape(-1))
         return ns, rew, done, {"th_ddot": thdd}
 
     def _task_struct(self):

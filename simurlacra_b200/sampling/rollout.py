@@ -1,0 +1,285 @@
+"""
+rollout() (pyrado/sampling/rollout.py:63-343) on the CUDA engine.
+
+Fused path (the hot one): when every wrapper of the chain fuses into the kernels and the policy has a CUDA forward
+pass, the WHOLE rollout -- reset, [domain randomization], and the loop {observe (+noise) -> policy -> [ActNorm] ->
+SimPyEnv.step} until done -- is ONE launch of the persistent-horizon kernel (`sre_rollout`), for all `num_envs`
+environments of the batch at once; the time-major record buffer is then cut into the reference's `StepSequence`s.
+
+Generic path: any other env chain / policy (custom wrappers, arbitrary callables, `no_reset`) runs the reference's loop;
+each `env.step` is a launch of the step kernel, the policy is evaluated as a torch module in between.
+
+A batch env (`num_envs > 1`) returns a list with one StepSequence per environment.
+"""
+import time
+from typing import Callable, List, Optional, Union
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+import simurlacra_b200 as pyrado
+
+from .. import _lib as L
+from .. import engine as E
+from ..environment_wrappers.base import EnvWrapper
+from ..environment_wrappers.domain_randomization import DomainRandWrapperBuffer, DomainRandWrapperLive
+from ..environment_wrappers.utils import all_envs, inner_env
+from ..environments.base import Env
+from ..environments.pysim.base import Fusion, SimPyEnv
+from ..environments.sim_base import SimEnv
+from ..policies.base import Policy
+from ..utils.data_types import RenderMode
+from .step_sequence import StepSequence
+
+HIDDEN_FIELD = {L.QCP: "th_ddot", L.QBB: "plate_angs"}  # name of the hidden-state column(s) in a StepSequence
+
+
+class CompiledChain:
+    """An env chain reduced to what the rollout kernel needs."""
+
+    def __init__(self, sim: SimPyEnv, fusion: Fusion, live_randomizer, buffer_wrappers):
+        self.sim, self.fusion, self.live_randomizer, self.buffer_wrappers = sim, fusion, live_randomizer, buffer_wrappers
+
+
+def compile_chain(env: Env) -> Optional[CompiledChain]:
+    """(inner SimPyEnv, Fusion, live randomizer, buffer DR wrappers) if the whole chain fuses, else None."""
+    sim = inner_env(env)
+    if not isinstance(sim, SimPyEnv):
+        return None
+    fusion, live, buffers = Fusion(), None, []
+    chain = [e for e in all_envs(env) if isinstance(e, EnvWrapper)]
+    for i, w in enumerate(chain):
+        below = chain[i + 1:]
+        if not w._fuse(fusion, any(b._alters_act for b in below), any(b._alters_obs for b in below)):
+            return None
+        if isinstance(w, DomainRandWrapperLive):
+            if live is not None:
+                return None  # two live randomizers: order-dependent, take the generic path
+            live = w.randomizer
+        elif isinstance(w, DomainRandWrapperBuffer):
+            buffers.append(w)
+    if sim._custom_init_space and type(sim.init_space).__name__ != "BoxSpace":
+        return None
+    return CompiledChain(sim, fusion, live, buffers)
+
+
+def _rollout_info(env: Env, sim, params_row: Optional[np.ndarray]) -> dict:
+    info = dict(env_name=env.name, env_spec=env.spec)
+    if isinstance(sim, SimEnv):
+        if params_row is not None and isinstance(sim, SimPyEnv):
+            dp = {k: float(params_row[i]) for i, k in enumerate(sim._param_names)}
+            for w in [e for e in all_envs(env) if isinstance(e, EnvWrapper)][::-1]:
+                w._set_wrapper_domain_param(dp)
+            info["domain_param"] = dp
+        else:
+            info["domain_param"] = env.domain_param
+    return info
+
+
+def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_format: str = "numpy",
+                           env_ids: Optional[np.ndarray] = None) -> List[StepSequence]:
+    """Cut the first episode of every lane out of the kernel's time-major record buffer (engine extension)."""
+    length = res["length"].cpu().numpy()
+    flags = res["row_flag"]
+    n = length.shape[0]
+    t_max = int(length.max()) + 1
+    to_host = (lambda t: t[:t_max].double().cpu().numpy()) if data_format == "numpy" else (lambda t: t[:t_max])
+    obs, act, act_app, rew, state = (to_host(res[k]) for k in ("obs", "act", "act_app", "rew", "state"))
+    hidden = to_host(res["hidden"]) if sim._dims["nh"] > 0 else None
+    done_flag = flags[:t_max].cpu().numpy()
+    params = res["params"].double().cpu().numpy()
+    out = []
+    for i in (range(n) if env_ids is None else env_ids):
+        ln = int(length[i])
+        fields = dict(rewards=rew[:ln, i], observations=obs[:ln + 1, i], actions=act[:ln, i],
+                      actions_applied=act_app[:ln, i], states=state[:ln + 1, i])
+        if hidden is not None:
+            h = hidden[:ln + 1, i]
+            fields[HIDDEN_FIELD.get(sim.kind, "hidden")] = h[:, 0] if h.shape[1] == 1 else h
+        done_last = bool(done_flag[ln - 1, i] == L.ROW_DONE)
+        out.append(StepSequence.from_records(fields, ln, dt, rollout_info=_rollout_info(env, sim, params[i]),
+                                             done_last=True, data_format=data_format))
+        out[-1].env_done = done_last  # engine extension: False if the row budget (not the env) ended the episode
+    return out
+
+
+def _fused_rollout(env, cc: CompiledChain, desc, max_steps, reset_kwargs, stop_on_done, data_format="numpy"):
+    sim = cc.sim
+    init_state = reset_kwargs.get("init_state")
+    domain_param = reset_kwargs.get("domain_param")
+    if domain_param is None:
+        for w in cc.buffer_wrappers:  # a buffer wrapper hands out its next parameter set(s)
+            n = sim.num_envs
+            sets = [w._next_set() for _ in range(n)] if isinstance(w.buffer, list) and n > 1 else [w._next_set()]
+            domain_param = sets[0] if len(sets) == 1 else {
+                k: np.array([float(np.asarray(s[k])) for s in sets]) for k in sets[0] if np.asarray(sets[0][k]).size == 1}
+    distr = None
+    if domain_param is not None:
+        env.domain_param = domain_param  # through the chain: wrappers take their own entries
+        cc = compile_chain(env)           # a wrapper parameter (e.g. obs_noise_std) may have changed
+    elif cc.live_randomizer is not None:
+        distr = cc.live_randomizer.table(sim._param_names)
+    cfg = sim._make_cfg(cc.fusion)
+    n, d = sim.num_envs, sim._dims
+    horizon = int(sim.max_steps) if np.isfinite(sim.max_steps) else None
+    if horizon is None:
+        raise pyrado.ValueErr(msg="The fused rollout needs a finite max_steps")
+    init = None
+    if init_state is not None:
+        init_state = np.asarray(init_state, dtype=np.float64) if not isinstance(init_state, torch.Tensor) else init_state
+        last = init_state.shape[-1]
+        if last not in (d["ds"], d["dinit"]):
+            raise pyrado.ShapeErr(given=init_state, expected_match=sim.state_space)
+        init = sim._to_dev(init_state, last)
+        if init.shape[0] == 1 and n > 1:
+            init = init.expand(n, -1).contiguous()
+    sim._episode += 1
+    res = E.rollout(cfg, desc, n, horizon + 1, device=sim.device, params=sim._params, distr=distr, init=init,
+                    seed=pyrado.device_seed(), env_offset=sim.env_offset, episode=sim._episode,
+                    stop_on_done=stop_on_done, auto_reset=False, record=True)
+    status = res["status"]
+    if n == 1 or bool((status != 0).any()):
+        bad = int(status.max())
+        if bad & (L.ST_NAN_OBS | L.ST_NAN_STATE):
+            raise pyrado.ValueErr(msg="At least one observation value is NaN!")
+        if bad & L.ST_NAN_ACT:
+            raise pyrado.ValueErr(msg="At least one action value is NaN!")
+    # leave the env where the rollout ended (env.state, curr_step), like the stepping loop would
+    sim._alloc()
+    ln = res["length"].long()
+    idx = torch.arange(n, device=sim.device)
+    sim._state.copy_(res["state"][ln, idx])
+    if d["nh"] > 0:
+        sim._hidden[:, : d["nh"]].copy_(res["hidden"][ln, idx])
+    sim._curr_step_t.copy_(res["length"])
+    sim._curr_step = int(res["length"][0]) if n == 1 else int(res["length"].max())
+    if distr is not None:
+        sim.set_param_tensor(res["params"])
+        first = res["params"][0].double().cpu().numpy()
+        for i, k in enumerate(sim._param_names):
+            sim._domain_param[k] = float(first[i])
+    return sequences_from_records(env, sim, res, sim.dt, data_format)
+
+
+def _hidden_of(sim):
+    if isinstance(sim, SimPyEnv) and sim._dims["nh"] > 0 and sim.hidden_state is not None:
+        return sim.hidden_state.clone()
+    return None
+
+
+def _generic_rollout(env, policy, eval, reset_kwargs, no_reset, stop_on_done, record_dts):
+    """The reference's loop (rollout.py:139-312); every env.step is a step-kernel launch."""
+    sim = inner_env(env)
+    n = getattr(sim, "num_envs", 1)
+    batch = n > 1
+    obs = (np.zeros(env.obs_space.shape) if not batch else torch.zeros(n, *env.obs_space.shape, device=sim.device)) \
+        if no_reset else env.reset(**reset_kwargs)
+    info0 = dict(env_name=env.name, env_spec=env.spec)
+    if isinstance(sim, SimEnv):
+        info0["domain_param"] = env.domain_param
+    if isinstance(policy, Policy):
+        policy.reset(**(dict(domain_param=env.domain_param) if isinstance(env, SimEnv) else dict()))
+        policy.eval() if eval else policy.train()
+    hist = dict(obs=[], act=[], act_app=[], rew=[], state=[], hidden=[], done=[], dt_policy=[], dt_step=[])
+    finished = torch.zeros(n, dtype=torch.bool, device=sim.device) if batch else False
+    pol_dev = next(iter(policy.parameters()), torch.zeros(0)).device if isinstance(policy, nn.Module) else None
+    steps = 0
+    while steps < env.max_steps and not (bool(finished.all()) if batch else (finished and stop_on_done)):
+        t0 = time.time()
+        obs_t = obs if isinstance(obs, torch.Tensor) else torch.from_numpy(np.asarray(obs))
+        if bool(torch.isnan(obs_t).any()):
+            raise pyrado.ValueErr(msg="At least one observation value is NaN!")
+        obs_to = obs_t.to(dtype=torch.get_default_dtype())
+        if pol_dev is not None:
+            obs_to = obs_to.to(pol_dev)
+        with torch.no_grad():
+            act_to = policy(obs_to)
+        if bool(torch.isnan(act_to).any()):
+            raise pyrado.ValueErr(msg="At least one action value is NaN!")
+        act = act_to.detach().to(sim.device) if batch else act_to.detach().cpu().numpy()
+        t1 = time.time()
+        state = env.state
+        hid = _hidden_of(sim)
+        obs_next, rew, done, _ = env.step(act)
+        act_app = env.limit_act(act)
+        t2 = time.time()
+        for k, v in (("obs", obs), ("act", act), ("act_app", act_app), ("rew", rew), ("state", state), ("hidden", hid),
+                     ("done", done), ("dt_policy", t1 - t0), ("dt_step", t2 - t1)):
+            hist[k].append(v)
+        obs = obs_next
+        steps += 1
+        finished = (finished | done) if batch and stop_on_done else (done if not batch else finished)
+    hist["obs"].append(obs)
+    hist["state"].append(env.state)
+    hist["hidden"].append(_hidden_of(sim))
+    if steps == 0:
+        raise pyrado.ShapeErr(msg="StepSequence must not be empty!")
+    hname = HIDDEN_FIELD.get(getattr(sim, "kind", None), "hidden")
+
+    def seq_for(i, ln):
+        pick = (lambda v: v) if not batch else (lambda v: v[i].double().cpu().numpy() if isinstance(v, torch.Tensor) else v)
+        data = dict(actions_applied=[pick(a) for a in hist["act_app"][:ln]], states=[pick(s) for s in hist["state"][:ln + 1]])
+        if hist["hidden"][0] is not None:
+            hs = [h[i if batch else 0].double().cpu().numpy() for h in hist["hidden"][:ln + 1]]
+            data[hname] = [h[0] if h.shape[0] == 1 else h for h in hs]
+        if record_dts:
+            data["dts_policy"], data["dts_step"] = hist["dt_policy"][:ln], hist["dt_step"][:ln]
+        return StepSequence(rewards=[float(pick(r)) for r in hist["rew"][:ln]],
+                            observations=[pick(o) for o in hist["obs"][:ln + 1]],
+                            actions=[pick(a) for a in hist["act"][:ln]], time=np.arange(ln + 1) * env.dt,
+                            rollout_info=info0, complete=True, **data)
+
+    if not batch:
+        return [seq_for(0, steps)]
+    done_mat = torch.stack(hist["done"]).cpu().numpy()  # [steps, n]
+    out = []
+    for i in range(n):
+        hit = np.flatnonzero(done_mat[:, i])
+        out.append(seq_for(i, int(hit[0]) + 1 if len(hit) and stop_on_done else steps))
+    return out
+
+
+def rollout(env: Env, policy: Union[nn.Module, Policy, Callable], eval: bool = False, max_steps: Optional[int] = None,
+            reset_kwargs: Optional[dict] = None, render_mode: RenderMode = RenderMode(), render_step: int = 1,
+            no_reset: bool = False, no_close: bool = False, record_dts: bool = False, stop_on_done: bool = True,
+            seed: Optional[int] = None, sub_seed: Optional[int] = None, sub_sub_seed: Optional[int] = None,
+            data_format: str = "numpy") -> Union[StepSequence, List[StepSequence]]:
+    """
+    Perform a rollout (i.e. sample a trajectory) in the given environment using the given policy.  Same signature as
+    the reference (rollout.py:63-78); rendering arguments are accepted and ignored (no graphics stack on this box).
+
+    :return: one `StepSequence` for a single env, a list with one `StepSequence` per env for a batch env
+    """
+    if not isinstance(env, Env):
+        raise pyrado.TypeErr(given=env, expected_type=Env)
+    if not isinstance(eval, bool):
+        raise pyrado.TypeErr(given=eval, expected_type=bool)
+    if not (isinstance(reset_kwargs, dict) or reset_kwargs is None):
+        raise pyrado.TypeErr(given=reset_kwargs, expected_type=dict)
+    if not isinstance(render_mode, RenderMode):
+        raise pyrado.TypeErr(given=render_mode, expected_type=RenderMode)
+    if max_steps is not None:
+        env.max_steps = max_steps
+    if seed is not None:
+        pyrado.set_seed(seed, sub_seed, sub_sub_seed)
+    reset_kwargs = dict() if reset_kwargs is None else reset_kwargs
+
+    cc = None if (no_reset or record_dts) else compile_chain(env)
+    desc = None
+    if cc is not None and isinstance(policy, Policy) and np.isfinite(env.max_steps):
+        desc = policy.engine_desc(cc.sim.device)
+    if cc is not None and desc is not None:
+        policy.reset(**(dict(domain_param=env.domain_param) if isinstance(env, SimEnv) else dict()))
+        policy.eval() if eval else policy.train()
+        ros = _fused_rollout(env, cc, desc, max_steps, reset_kwargs, stop_on_done, data_format)
+    else:
+        ros = _generic_rollout(env, policy, eval, reset_kwargs, no_reset, stop_on_done, record_dts)
+    if not no_close:
+        env.close()
+    return ros[0] if getattr(inner_env(env), "num_envs", 1) == 1 else ros
+
+
+def after_rollout_query(env: Env, policy: Policy, rollout: StepSequence) -> tuple:
+    """Non-interactive stand-in for the reference's console prompt (rollout.py:1209-1299): always "continue"."""
+    return False, None, None

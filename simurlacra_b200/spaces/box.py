@@ -68,6 +68,12 @@ class BoxSpace(Space):
         return np.random.uniform(lo, up)
 
     def project_to(self, ele: np.ndarray) -> np.ndarray:
+        if hasattr(ele, "clamp") and hasattr(ele, "device"):  # batch of elements as a torch tensor [N, *shape]
+            import torch
+
+            lo = torch.as_tensor(self.bound_lo, dtype=ele.dtype, device=ele.device)
+            up = torch.as_tensor(self.bound_up, dtype=ele.dtype, device=ele.device)
+            return torch.maximum(torch.minimum(ele, up), lo)
         if not isinstance(ele, np.ndarray):
             raise TypeErr(given=ele, expected_type=np.ndarray)
         return ele if self.contains(ele) else np.clip(ele, self.bound_lo, self.bound_up)

@@ -1,0 +1,284 @@
+"""
+CPU tests of the host-side mirror of the reference API (no CUDA device needed, no compute calls): seed hashing,
+spaces, task descriptors, StepSequence, wrapper-chain logic, randomizer tables, sharding arithmetic, and the two-process
+gloo test of the statistics all-reduce / ragged all-gather that the multi-GPU sampler uses.
+Reference known answers: Pyrado/tests/test_set_seed.py:34-55, Pyrado/tests/test_tasks.py:82-99 (in test_oracle_golden).
+"""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import simurlacra_b200 as pyrado
+from conftest import ROOT
+from simurlacra_b200 import _lib as L
+from simurlacra_b200.domain_randomization import (BernoulliDomainParam, DomainRandomizer, NormalDomainParam,
+                                                   UniformDomainParam)
+from simurlacra_b200.domain_randomization.default_randomizers import (create_default_randomizer,
+                                                                       create_default_randomizer_qbb,
+                                                                       create_default_randomizer_qq,
+                                                                       create_zero_var_randomizer)
+from simurlacra_b200.environment_wrappers import (ActNormWrapper, DomainRandWrapperBuffer, DomainRandWrapperLive,
+                                                   EnvWrapperAct, GaussianObsNoiseWrapper, inner_env, remove_env,
+                                                   typed_env)
+from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamSim
+from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
+from simurlacra_b200.environments.pysim.quanser_cartpole import QCartPoleSwingUpSim
+from simurlacra_b200.environments.pysim.quanser_qube import QQubeSwingUpSim
+from simurlacra_b200.policies import FeatureStack, FNNPolicy, IdlePolicy, LinearPolicy
+from simurlacra_b200.policies.features import const_feat, identity_feat, squared_feat
+from simurlacra_b200.sampling import sharding
+from simurlacra_b200.sampling.rollout import compile_chain
+from simurlacra_b200.sampling.step_sequence import StepSequence, discounted_reverse_cumsum, gae_returns
+
+_SEED_KA = {0: [813134492, 4276188331, 229607210, 3918913762], 1: [532102107, 2754337450, 713485941, 3511146676]}
+# all 18 vectors of Pyrado/tests/test_set_seed.py:34-55: per base seed the answers for (sub, subsub) hashing to
+# "b-0-0", "b-0-1", "b-1-0", "b-1-1"; None counts as 0
+SEED_VECTORS = [((b, s, ss), _SEED_KA[b][2 * int(bool(s)) + int(bool(ss))])
+                for b in (0, 1) for s in (None, 0, 1) for ss in (None, 0, 1)]
+
+
+@pytest.mark.parametrize("triple,expected", SEED_VECTORS)
+def test_seed_hash_known_answers(triple, expected):
+    assert pyrado.seed_hash(*triple) == expected
+    assert pyrado.set_seed(*triple) == expected
+    assert pyrado.device_seed() == expected and pyrado.get_base_seed() == triple[0]
+
+
+def test_env_ctor_errors_and_spaces():
+    with pytest.raises(pyrado.ValueErr):
+        QQubeSwingUpSim(dt=-0.1)
+    with pytest.raises(pyrado.TypeErr):
+        QQubeSwingUpSim(dt="a")
+    with pytest.raises(pyrado.ValueErr):
+        QQubeSwingUpSim(dt=0.01, max_steps=0)
+    env = QQubeSwingUpSim(dt=1 / 250.0, max_steps=600)
+    assert env.obs_space.flat_dim == 6 and env.act_space.flat_dim == 1 and env.state_space.flat_dim == 4
+    assert env.spec.obs_space is env.obs_space
+    assert set(env.supported_domain_param) == set(env.get_nominal_domain_param())
+    for _ in range(100):  # Pyrado/tests/test_environments.py:140-148
+        assert env.init_space.contains(env.init_space.sample_uniform())
+    env.max_steps = 10
+    assert env.max_steps == 10
+    with pytest.raises(pyrado.ValueErr):
+        env.max_steps = 0
+
+
+def test_domain_param_set_get_roundtrip_and_dependent_spaces():
+    """Pyrado/tests/test_domain_randomization.py:194-205: set every key, read it back."""
+    for env in (QQubeSwingUpSim(dt=0.01), QCartPoleSwingUpSim(dt=0.01, long=True), QBallBalancerSim(dt=0.01),
+                BallOnBeamSim(dt=0.01)):
+        nom = env.get_nominal_domain_param() if not isinstance(env, QCartPoleSwingUpSim) else env.domain_param
+        for k, v in nom.items():
+            new = v * 1.1 + 0.01
+            env.domain_param = {k: new}
+            assert abs(env.domain_param[k] - new) < 5e-4
+    cp = QCartPoleSwingUpSim(dt=0.01)
+    cp.domain_param = dict(rail_length=1.0)
+    assert cp.state_space.bound_up[0] == pytest.approx(0.5 - 0.15)
+    bob = BallOnBeamSim(dt=0.01)
+    bob.domain_param = dict(beam_length=4.0)
+    assert bob.state_space.bound_up[0] == pytest.approx(2.0)
+
+
+def test_wild_init_string_semantics():
+    wide = QCartPoleSwingUpSim(dt=0.01, wild_init="True").init_space.bound_up
+    narrow = QCartPoleSwingUpSim(dt=0.01, wild_init="False").init_space.bound_up
+    other = QCartPoleSwingUpSim(dt=0.01, wild_init=True).init_space.bound_up  # a bool takes the else branch
+    assert wide[1] == pytest.approx(np.pi) and wide[0] == pytest.approx(0.25)
+    assert narrow[1] == pytest.approx(2 / 180 * np.pi)
+    assert other[0] == pytest.approx(0.02) and other[1] == pytest.approx(np.pi)
+
+
+def test_domain_param_classes_and_randomizer_table():
+    with pytest.raises(ValueError):
+        NormalDomainParam(name="m", mean=1.0, std=0.0)
+    with pytest.raises(ValueError):
+        UniformDomainParam(name="m", mean=1.0, halfspan=0.0)
+    with pytest.raises(ValueError):
+        BernoulliDomainParam(name="b", val_0=0, val_1=1, prob_1=1.5)
+    b = BernoulliDomainParam(name="b", val_0=2.0, val_1=4.0, prob_1=0.25)
+    assert b.mean == pytest.approx(2.5)
+    n = NormalDomainParam(name="m", mean=1.0, std=0.2, clip_lo=1e-3)
+    n.adapt("std", 0.1)
+    assert n.std == 0.1
+    with pytest.raises(pyrado.KeyErr):
+        n.adapt("halfspan", 0.1)
+    r = create_default_randomizer_qq()
+    assert len(r.domain_params) == 9 and "gravity_const" in str(r)
+    env = QQubeSwingUpSim(dt=0.01)
+    tab = r.table(env._param_names)
+    assert tab._n == 9
+    assert [tab[i].param_index for i in range(9)] == [env._param_names.index(dp.name) for dp in r.domain_params]
+    assert tab[0].kind == L.DISTR_NORMAL and tab[0].a == pytest.approx(9.81) and tab[0].b == pytest.approx(0.981)
+    assert tab[0].clip_lo == pytest.approx(1e-3)
+    q = create_default_randomizer_qbb()
+    assert len(q.domain_params) == 20
+    kinds = [dp._distr_kind for dp in q.domain_params]
+    assert kinds.count("normal") == 10 and kinds.count("uniform") == 10
+    r.rescale_distr_param("std", 0.5)
+    assert r.domain_params[0].std == pytest.approx(0.4905)
+    z = create_zero_var_randomizer(ActNormWrapper(env))
+    assert z.domain_params[0].std == pytest.approx(0.981e-4)
+    assert type(create_default_randomizer(QCartPoleSwingUpSim(dt=0.01))).__name__ == "DomainRandomizer"
+    with pytest.raises(pyrado.TypeErr):
+        DomainRandomizer("not a param")
+
+
+def test_wrapper_chain_delegation_and_fusion():
+    env = QQubeSwingUpSim(dt=1 / 250.0, max_steps=600)
+    an = ActNormWrapper(env)
+    assert np.all(an.act_space.bound_up == 1) and np.all(an.act_space.bound_lo == -1)
+    assert an._process_act(np.array([0.5]))[0] == pytest.approx(2.25)  # lb + (a + 1)(ub - lb)/2 with +-4.5 V
+    assert float(an._process_act_tensor(torch.tensor([[1.0]]))[0, 0]) == pytest.approx(4.5)
+    noisy = GaussianObsNoiseWrapper(an, noise_std=0.01 * np.ones(6))
+    with pytest.raises(pyrado.ShapeErr):
+        GaussianObsNoiseWrapper(an, noise_std=np.ones(3))
+    dr = DomainRandWrapperLive(noisy, create_default_randomizer_qq())
+    assert inner_env(dr) is env and typed_env(dr, ActNormWrapper) is an and dr.name == "qq-su"
+    assert dr.max_steps == 600 and dr.dt == pytest.approx(0.004)
+    dp = dr.domain_param
+    assert "obs_noise_std" in dp and dp["gravity_const"] == pytest.approx(9.81)
+    dr.domain_param = dict(obs_noise_std=0.5 * np.ones(6), gravity_const=9.0)
+    assert noisy._std[0] == 0.5 and env.domain_param["gravity_const"] == 9.0
+    cc = compile_chain(dr)
+    assert cc is not None and cc.sim is env and cc.fusion.act_norm and cc.fusion.noise_std[0] == 0.5
+    assert cc.live_randomizer is dr.randomizer
+    cfg = env._make_cfg(cc.fusion)
+    assert cfg.act_norm == 1 and cfg.obs_noise == 1 and cfg.noise_std[5] == 0.5 and cfg.kind == L.QQ
+    stripped = remove_env(dr, GaussianObsNoiseWrapper)
+    assert typed_env(stripped, GaussianObsNoiseWrapper) is None and inner_env(stripped) is env
+    assert typed_env(dr, GaussianObsNoiseWrapper) is noisy  # the original chain is untouched
+
+    class Scale(EnvWrapperAct):  # a user wrapper the kernels do not know
+        def _process_act(self, act):
+            return 2 * act
+
+    assert compile_chain(Scale(an)) is None                      # not fusable -> generic stepping path
+    assert compile_chain(ActNormWrapper(Scale(env))) is None
+    with pytest.raises(pyrado.TypeErr):
+        DomainRandWrapperLive(env, "nope")
+    buf = DomainRandWrapperBuffer(env, None)
+    buf.buffer = [dict(gravity_const=1.0), dict(gravity_const=2.0)]
+    buf._ring_idx = 0
+    assert buf._next_set()["gravity_const"] == 1.0 and buf._next_set()["gravity_const"] == 2.0 and buf.ring_idx == 0
+    with pytest.raises(pyrado.ValueErr):
+        DomainRandWrapperBuffer(env, None, selection="zigzag")
+
+
+def test_policies_descriptors_and_torch_forward():
+    env = QQubeSwingUpSim(dt=0.01)
+    torch.manual_seed(0)
+    pol = FNNPolicy(env.spec, hidden_sizes=[16, 16], hidden_nonlin=torch.tanh)
+    assert pol.num_param == 6 * 16 + 16 + 16 * 16 + 16 + 16 + 1
+    assert pol(torch.zeros(6)).shape == (1,) and pol(torch.zeros(3, 6)).shape == (3, 1)  # test_policies.py:361-455
+    v = pol.param_values.clone()
+    pol.param_values = v * 0 + 0.5
+    assert torch.all(pol.param_values == 0.5)
+    with pytest.raises(pyrado.ShapeErr):
+        pol.param_values = torch.zeros(3)
+    assert pol.net.engine_codes() == (0, 0)
+    assert FNNPolicy(env.spec, [8], torch.relu, output_nonlin=torch.tanh).net.engine_codes() == (1, 1)
+    assert FNNPolicy(env.spec, [8], torch.sigmoid).net.engine_codes() is None  # no kernel -> generic path
+    fork = FNNPolicy(QCartPoleSwingUpSim(dt=0.01).spec._replace(obs_space=QCartPoleSwingUpSim(dt=0.01).state_space),
+                     [16], torch.tanh, cartpole_feats=True)
+    assert fork.net.sizes[0] == 5 and fork(torch.zeros(2, 4)).shape == (2, 1)
+    lin = LinearPolicy(env.spec, FeatureStack(const_feat, identity_feat, squared_feat))
+    assert lin.num_active_feat == 13 and lin.features.engine_codes() == ["const", "identity", "squared"]
+    assert lin(torch.ones(6)).shape == (1,) and lin(torch.ones(4, 6)).shape == (4, 1)
+    assert FeatureStack(identity_feat, lambda x: x).engine_codes() is None
+    assert torch.all(IdlePolicy(env.spec)(torch.ones(5, 6)) == 0)
+    with pytest.raises(pyrado.TypeErr):
+        LinearPolicy(env.spec, "feats")
+
+
+def test_step_sequence_container():
+    rng = np.random.RandomState(0)
+    ro = StepSequence(rewards=rng.rand(5), observations=rng.randn(6, 3), actions=rng.randn(5, 1), states=rng.randn(6, 2),
+                      rollout_info=dict(env_name="x"))
+    assert len(ro) == 5 and ro.done[-1] and list(ro.rollout_bounds) == [0, 5] and ro.rollout_count == 1
+    assert ro[2].reward == ro.rewards[2] and np.all(ro[2].next_observation == ro.observations[3]) and not ro[2].done
+    assert ro[-1].done and np.all(ro[1:3].observations == ro.observations[1:3])
+    with pytest.raises(pyrado.ShapeErr):
+        StepSequence(rewards=[], observations=[], actions=[])
+    with pytest.raises(pyrado.ShapeErr):
+        ro.add_data("bad", np.zeros(3))
+    with pytest.raises(pyrado.KeyErr):
+        ro.add_data("states", np.zeros(5))
+    ro.add_data("values", rng.rand(6))
+    c = StepSequence.concat([ro, ro])
+    assert c.length == 10 and list(c.rollout_bounds) == [0, 5, 10] and c.rollout_info == dict(env_name="x")
+    assert np.all(c.get_rollout(1).rewards == ro.rewards) and len(list(c.iterate_rollouts())) == 2
+    assert c.observations.shape == (10, 3)  # the final observation of every part is dropped
+    assert ro.undiscounted_return() == pytest.approx(ro.rewards.sum())
+    assert ro.discounted_return(0.9) == pytest.approx(np.dot(ro.rewards, 0.9 ** np.arange(5)))
+    y = discounted_reverse_cumsum(ro.rewards, 0.9)
+    assert y[0] == pytest.approx(ro.discounted_return(0.9)) and y[-1] == pytest.approx(ro.rewards[-1])
+    adv = gae_returns(ro, gamma=0.99, lamb=1.0)  # lambda = 1: discounted return minus the baseline (+ bootstrap)
+    assert adv[-1] == pytest.approx(ro.rewards[-1] - ro.values[4])
+    sizes = [b.length for b in c.split_ordered_batches(batch_size=4)]
+    assert sizes == [4, 4, 2] and sum(b.length for b in c.split_shuffled_batches(3)) == 10
+    assert all(b.rollout_count >= 1 for b in c.split_shuffled_batches(4, complete_rollouts=True))
+    StepSequence.pad(ro, 8)
+    assert ro.length == 8 and ro.observations.shape == (9, 3) and list(ro.rollout_bounds) == [0, 8] and not ro.done[-1]
+    ro.torch()
+    assert isinstance(ro.rewards, torch.Tensor) and ro.data_format == "torch"
+    ro.numpy()
+    assert isinstance(ro.rewards, np.ndarray)
+
+
+def test_shard_ranges_cover_and_balance():
+    for n in (0, 1, 7, 8, 1000, 1 << 20):
+        for ws in (1, 2, 3, 4, 8):
+            blocks = [sharding.shard_range(n, r, ws) for r in range(ws)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(ws - 1))
+            sizes = [b - a for a, b in blocks]
+            assert max(sizes) - min(sizes) <= 1
+    s = torch.tensor([4, 10.0, 30.0, 40, 40, 1, 1.0, 4.0], dtype=torch.float64)
+    d = sharding.summarize(s)
+    assert d["avg_return"] == 2.5 and d["std_return"] == pytest.approx((7.5 - 6.25) ** 0.5) and d["avg_rollout_len"] == 10
+
+
+_GLOO_WORKER = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["SRE_ROOT"])
+from simurlacra_b200.sampling import sharding
+dist.init_process_group("gloo")
+rank, ws = sharding.world()
+n_total = 7
+lo, hi = sharding.shard_range(n_total, rank, ws)
+ret = torch.arange(lo, hi, dtype=torch.float64) + 1.0          # "returns" of this rank's rollouts
+stats = torch.tensor([hi - lo, ret.sum(), (ret ** 2).sum(), 10.0 * (hi - lo), 10.0 * (hi - lo), 0.0, ret.min(), ret.max()],
+                     dtype=torch.float64)
+sharding.allreduce_stats(stats)
+assert stats.tolist() == [7.0, 28.0, 140.0, 70.0, 70.0, 0.0, 1.0, 7.0], stats
+full = sharding.allgather_ragged(ret, n_total)
+assert full.tolist() == [1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0], full
+lin = torch.nn.Linear(3, 2)
+with torch.no_grad():
+    lin.weight.fill_(float(rank + 1))
+sharding.broadcast_policy(lin, src=0)
+assert float(lin.weight[0, 0]) == 1.0
+dist.barrier(); dist.destroy_process_group()
+print("rank", rank, "ok")
+"""
+
+
+def test_multi_rank_statistics_allreduce_gloo(tmp_path):
+    """world_size 2 on CPU (gloo): the sampler's statistics all-reduce, ragged all-gather and policy broadcast."""
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, SRE_ROOT=ROOT, OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                       capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
