@@ -28,6 +28,12 @@ def device_seed() -> int:
     return _DEVICE_SEED
 
 
+def set_device_seed(seed: int):
+    """Key of the device-side Philox streams (engine extension; `set_seed` sets it to the hashed seed)."""
+    global _DEVICE_SEED
+    _DEVICE_SEED = int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
 def seed_hash(seed: int, sub_seed: Optional[int] = None, sub_sub_seed: Optional[int] = None) -> int:
     """md5("base-sub-subsub") mod 2^32 (pyrado/__init__.py:168); pinned by Pyrado/tests/test_set_seed.py:34-55."""
     sub_seed = 0 if sub_seed is None else sub_seed

@@ -2,10 +2,11 @@
 DomainRandWrapper, DomainRandWrapperLive, DomainRandWrapperBuffer, MetaDomainRandWrapper
 (pyrado/environment_wrappers/domain_randomization.py:47-300).
 
-Single env: the reference's flow -- `randomizer.randomize(1)` -> `get_params(fmt="dict", dtype="numpy")` ->
-`reset(domain_param=...)`.  Batch of envs: one launch of the Philox sampler writes a fresh parameter set per env
-straight into the env's `[num_envs, dp]` device tensor (keyed (seed, global env index, episode), the key the
-persistent rollout kernel uses when it samples the same randomizer in-flight).
+The reference's flow is `randomizer.randomize(1)` -> `get_params(fmt="dict", dtype="numpy")` ->
+`reset(domain_param=...)`.  Around a `SimPyEnv` one launch of the Philox sampler writes a fresh parameter set per env
+straight into the env's `[num_envs, dp]` device tensor, keyed (seed, global env index, episode) -- the key the
+persistent rollout kernel uses when it samples the same randomizer in-flight, so stepping through the wrapper and
+the fused rollout see the same parameters.  Around any other SimEnv the reference's dict flow is used.
 """
 from random import randint
 from typing import List, Mapping, Optional, Tuple, Union
@@ -89,7 +90,7 @@ class DomainRandWrapperLive(DomainRandWrapper):
     def _reset_chain(self, init_state, domain_param, fusion):
         if domain_param is None:
             sim = inner_env(self)
-            if isinstance(sim, SimPyEnv) and sim.num_envs > 1:
+            if isinstance(sim, SimPyEnv):
                 sim.randomize_params(self._randomizer)  # one kernel launch, parameters stay on the device
                 extra = [n for n in self._randomizer.names() if n not in sim._param_names]
                 if extra:  # wrapper-owned entries (e.g. obs_noise_std): one value for the whole batch

@@ -36,7 +36,7 @@ class BallOnBeamSim(SimPyEnv):
         self._act_space = BoxSpace(-max_act, max_act, labels=["tau"])
 
     def _create_task(self, task_args: dict):  # :100-108
-        state_des = task_args.get("state_des", np.zeros(4))
+        state_des = np.asarray(task_args.get("state_des", np.zeros(4)), dtype=np.float64)
         Q = task_args.get("Q", np.diag([1e5, 1e3, 1e3, 1e2]))
         R = task_args.get("R", np.eye(self.spec.act_space.flat_dim))
         return DesStateTask(self.spec, state_des,

@@ -29,7 +29,7 @@ class OneMassOscillatorSim(SimPyEnv):
         self._act_space = BoxSpace(-np.array([max_state[0] * k]), np.array([max_state[0] * k]), labels=["F"])
 
     def _create_task(self, task_args: dict):  # :68-79
-        state_des = task_args.get("state_des", np.zeros(2))
+        state_des = np.asarray(task_args.get("state_des", np.zeros(2)), dtype=np.float64)
         Q = task_args.get("Q", np.diag([1e1, 1e-2]))
         R = task_args.get("R", np.diag([1e-6]))
         return FinalRewTask(DesStateTask(self.spec, state_des, QuadrErrRewFcn(Q, R)), factor=1e3,

@@ -59,7 +59,7 @@ class QBallBalancerSim(SimPyEnv):
         self._act_space = BoxSpace(-MAX_ACT_QBB, MAX_ACT_QBB, shape=(2,), labels=["V_x", "V_y"])
 
     def _create_task(self, task_args: dict):  # :121-131
-        state_des = task_args.get("state_des", np.zeros(8))
+        state_des = np.asarray(task_args.get("state_des", np.zeros(8)), dtype=np.float64)
         Q = task_args.get("Q", np.diag([1e0, 1e0, 5e3, 5e3, 1e-2, 1e-2, 5e-1, 5e-1]))
         R = task_args.get("R", np.diag([1e-2, 1e-2]))
         return DesStateTask(self.spec, state_des,

@@ -69,7 +69,7 @@ class QCartPoleSwingUpSim(SimPyEnv):
             self._init_space = BoxSpace(-mi, mi, labels=["x", "theta", "x_dot", "theta_dot"])
 
     def _create_task(self, task_args: dict):  # :573-588
-        state_des = task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0]))
+        state_des = np.asarray(task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0])), dtype=np.float64)
         Q = task_args.get("Q", np.diag([3e-1, 5e-1, 5e-3, 1e-3]))
         R = task_args.get("R", np.diag([1e-3]))
         return RadiallySymmDesStateTask(self.spec, state_des, ExpQuadrErrRewFcn(Q, R), idcs=[1])

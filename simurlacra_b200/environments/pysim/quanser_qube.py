@@ -36,7 +36,7 @@ class QQubeSwingUpSim(SimPyEnv):
         self._act_space = BoxSpace(-MAX_ACT_QQ, MAX_ACT_QQ, shape=(1,), labels=["V"])
 
     def _create_task(self, task_args: dict):  # :183-188
-        state_des = task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0]))
+        state_des = np.asarray(task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0])), dtype=np.float64)
         Q = task_args.get("Q", np.diag([1.0, 1.0, 2e-2, 5e-3]))
         R = task_args.get("R", np.diag([4e-3]))
         return RadiallySymmDesStateTask(self.spec, state_des, ExpQuadrErrRewFcn(Q, R), idcs=[1])

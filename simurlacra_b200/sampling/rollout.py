@@ -262,7 +262,15 @@ def rollout(env: Env, policy: Union[nn.Module, Policy, Callable], eval: bool = F
     if max_steps is not None:
         env.max_steps = max_steps
     if seed is not None:
-        pyrado.set_seed(seed, sub_seed, sub_sub_seed)
+        pyrado.set_seed(seed, sub_seed, sub_sub_seed)  # host generators, like the reference
+        # Device streams: rollout `sub_sub_seed` of sampling round `sub_seed` is lane `sub_sub_seed` of the Philox
+        # stream keyed seed_hash(seed, sub_seed) -- the key ParallelRolloutSampler gives to its lane of that index,
+        # so that sequential rollouts equal the sampler's (Pyrado/tests/test_sampling.py:570-587)
+        sim0 = inner_env(env)
+        if isinstance(sim0, SimPyEnv):
+            pyrado.set_device_seed(pyrado.seed_hash(seed, sub_seed, 0))
+            sim0.env_offset = (sub_sub_seed or 0) * sim0.num_envs
+            sim0._episode = -1  # the reset below advances it to episode 0
     reset_kwargs = dict() if reset_kwargs is None else reset_kwargs
 
     cc = None if (no_reset or record_dts) else compile_chain(env)
