@@ -71,6 +71,11 @@ extern "C" {
 #define SRE_POL_LINEAR 2  /* policies/feed_back/linear.py:41 + policies/features.py:42 */
 #define SRE_POL_IDLE 3    /* policies/feed_forward/dummy.py (IdlePolicy): zero action */
 
+/* sre_policy.precision */
+#define SRE_PREC_FP32 0   /* FP32 FMA on the CUDA cores (bias first, inputs ascending) */
+#define SRE_PREC_TF32X3 1 /* tcgen05 tensor cores, 3 x TF32 split (hi*hi + hi*lo + lo*hi): fp32-level accuracy */
+#define SRE_PREC_TF32 2   /* tcgen05 tensor cores, single TF32 pass (about 1e-3 relative) */
+
 /* feature functions of the Linear policy, policies/features.py:127-175 */
 #define SRE_FEAT_CONST 0
 #define SRE_FEAT_IDENTITY 1
@@ -174,6 +179,7 @@ typedef struct sre_policy {
     int32_t hidden_nonlin;            /* 0 tanh, 1 relu, 2 identity */
     int32_t output_nonlin;            /* 0 none, 1 tanh */
     int32_t cartpole_feats;           /* the fork's FNNPolicy input transform, fnn.py:214-218 */
+    int32_t precision;                /* SRE_PREC_*: arithmetic of the 64x64 hidden layer (float builds, [in,64,64,out] tanh) */
     const float *weights;             /* device; torch layout W[out][in], bias[out], layers concatenated */
     int64_t n_weights;
 } sre_policy;

@@ -83,6 +83,8 @@ int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp) {
     kp.hidden_nonlin = pol->hidden_nonlin;
     kp.output_nonlin = pol->output_nonlin;
     kp.cartpole_feats = pol->cartpole_feats;
+    SRE_CHECK_ARG(pol->precision >= 0 && pol->precision <= SRE_PREC_TF32, SRE_E_POLICY, "unknown precision %d", pol->precision);
+    kp.precision = pol->precision;
     kp.weights = pol->weights;
     kp.n_weights = pol->n_weights;
     return 0;

@@ -14,7 +14,7 @@ struct KPolicy {
     int sizes[SRE_MAX_LAYERS + 1];
     int n_feats;
     int feats[SRE_MAX_FEATS];
-    int hidden_nonlin, output_nonlin, cartpole_feats;
+    int hidden_nonlin, output_nonlin, cartpole_feats, precision;
     const float *weights;  // device, torch layout
     long long n_weights;
     int smem_floats;  // size of the staged (re-laid-out) copy

@@ -1,0 +1,264 @@
+// sre_policy_tc.cuh -- FNN [IN, 64, 64, OUT] (tanh, linear output) with the 64x64 hidden layer on the 5th-generation
+// tensor cores (tcgen05 + TMEM), hand-written PTX for sm_100a.  Policy of policies/feed_back/fnn.py:138-160.
+//
+// A CTA of 128 threads owns 128 environments = the M = 128 rows of one UMMA tile:
+//   layer 1  (IN <= 8 inputs)   thread-per-env FFMA, weights broadcast from shared memory
+//   tanh, split h1 = hi + lo    hi = h1 with the low 13 mantissa bits cleared (a TF32 number), lo = h1 - hi (exact)
+//   A tiles  [128 x 64] tf32    each thread writes ITS row into the canonical K-major SWIZZLE_128B layout (conflict-
+//                               free 128-bit stores: the swizzle XORs the 16-byte chunk index with row % 8)
+//   layer 2  tcgen05.mma kind::tf32, M = 128, N = 64, K = 8 per instruction, one elected thread issues
+//            D  = A_lo * B_hi^T + A_hi * B_lo^T + A_hi * B_hi^T     (3 x TF32 split: fp32-level accuracy, the dropped
+//            term lo*lo is < 2^-22 relative), accumulators fp32 in TMEM (64 columns), tcgen05.commit -> mbarrier
+//   epilogue tcgen05.ld 32x32b: thread r reads row r (its own env): + b2, tanh, layer 3 as 64 FFMA per output
+// B = W2 (torch layout W[out][in] IS the K-major [N x K] operand), split hi / lo once per CTA at staging.
+// With SINGLE_PASS only A_hi * B_hi^T is issued (plain TF32, ~1e-3 relative): offered for throughput studies.
+#pragma once
+#include "sre_policy.cuh"
+
+namespace sre {
+
+SRE_DEV uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+SRE_DEV void st_shared_v4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// UMMA shared-memory matrix descriptor, K-major, SWIZZLE_128B (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+// start address >> 4 in [0,14), LBO (ignored for swizzled K-major, 1) in [16,30), SBO = 8 rows * 128 B = 1024 >> 4
+// in [32,46), version 1 in [46,48), layout type SWIZZLE_128B = 2 in [61,64)
+SRE_DEV uint64_t umma_desc_k_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// instruction descriptor (InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10), both K-major,
+// N >> 3 at [17,23), M >> 4 at [24,29)
+constexpr uint32_t UMMA_IDESC_TF32_M128_N64 = (1u << 4) | (2u << 7) | (2u << 10) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
+
+SRE_DEV void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+SRE_DEV void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+SRE_DEV void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+SRE_DEV void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        ::"r"(bar), "r"(parity)
+        : "memory");
+}
+SRE_DEV void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+SRE_DEV void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+SRE_DEV void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// 16 consecutive fp32 accumulator columns of this thread's TMEM lane
+SRE_DEV void tmem_ld16(uint32_t taddr, float *v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
+SRE_DEV void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC {
+    static constexpr int HID = 64;
+    static constexpr int THREADS = 128;
+    static constexpr int TMEM_COLS = 64;
+    // shared memory (bytes from a 1024-aligned base)
+    static constexpr int A_KB = 128 * 128;  // one K-block (32 tf32 = 128 B per row) of the A tile
+    static constexpr int B_KB = 64 * 128;
+    static constexpr int OFF_A_HI = 0;
+    static constexpr int OFF_A_LO = OFF_A_HI + 2 * A_KB;
+    static constexpr int OFF_B_HI = OFF_A_LO + 2 * A_KB;
+    static constexpr int OFF_B_LO = OFF_B_HI + 2 * B_KB;
+    static constexpr int OFF_W1T = OFF_B_LO + 2 * B_KB;          // float [IN][HID], prescaled
+    static constexpr int OFF_B1 = OFF_W1T + IN * HID * 4;        // float [HID], prescaled
+    static constexpr int OFF_B2 = OFF_B1 + HID * 4;              // float [HID], prescaled
+    static constexpr int OFF_W3 = OFF_B2 + HID * 4;              // float [OUT][HID]
+    static constexpr int OFF_B3 = OFF_W3 + OUT * HID * 4;        // float [OUT] (padded to 16 B)
+    static constexpr int OFF_BAR = OFF_B3 + 16;                  // mbarrier (8 B) + TMEM base address (4 B)
+    static constexpr int SMEM_BYTES = OFF_BAR + 16 + 1024;       // + slack for the manual 1024-byte alignment
+    static constexpr float PRE = SRE_TANH_PRESCALE;              // folded into W1, b1, W2, b2 (tanh_prescaled)
+
+    struct Ctx {
+        uint32_t base;      // shared-memory address of the aligned block
+        uint32_t tmem;      // TMEM base (lane 0, first column)
+        uint32_t parity;    // phase of the mbarrier
+        const float *gen;   // generic pointer to the aligned block (for ld.shared through C++)
+    };
+
+    SRE_DEV static uint32_t tf32_hi(float x) { return __float_as_uint(x) & 0xFFFFE000u; }
+
+    // byte offset of element (row, k) inside an operand whose K-blocks are `kb_bytes` apart
+    SRE_DEV static uint32_t sw_off(int row, int k, int kb_bytes) {
+        return (uint32_t)((k >> 5) * kb_bytes + row * 128 + ((((k & 31) >> 2) ^ (row & 7)) << 4) + ((k & 3) << 2));
+    }
+
+    // Called by all THREADS threads of the CTA once: stage the weights, allocate TMEM, init the barrier.
+    SRE_DEV static void setup(Ctx &c, unsigned char *smem_raw, const float *__restrict__ w) {
+        const uint32_t raw = smem_u32(smem_raw);
+        const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
+        c.base = raw + pad;
+        c.gen = reinterpret_cast<const float *>(smem_raw + pad);
+        c.parity = 0;
+        float *g = const_cast<float *>(c.gen);
+        const float *W1 = w, *b1 = W1 + IN * HID, *W2 = b1 + HID, *b2 = W2 + HID * HID, *W3 = b2 + HID,
+                    *b3 = W3 + OUT * HID;
+        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) g[OFF_W1T / 4 + (i % IN) * HID + i / IN] = PRE * W1[i];
+        for (int i = threadIdx.x; i < HID; i += blockDim.x) {
+            g[OFF_B1 / 4 + i] = PRE * b1[i];
+            g[OFF_B2 / 4 + i] = PRE * b2[i];
+        }
+        for (int i = threadIdx.x; i < OUT * HID; i += blockDim.x) g[OFF_W3 / 4 + i] = W3[i];
+        for (int i = threadIdx.x; i < 4; i += blockDim.x) g[OFF_B3 / 4 + i] = i < OUT ? b3[i] : 0.f;
+        for (int i = threadIdx.x; i < HID * HID; i += blockDim.x) {
+            const int n = i / HID, k = i % HID;  // W2[n][k]: output n, input k
+            const float v = PRE * W2[i];
+            const float hi = __uint_as_float(tf32_hi(v));
+            const uint32_t off = sw_off(n, k, B_KB);
+            g[(OFF_B_HI + off) / 4] = hi;
+            g[(OFF_B_LO + off) / 4] = v - hi;
+        }
+        if (threadIdx.x == 0) mbar_init(c.base + OFF_BAR, 1);
+        if (threadIdx.x < 32) {  // one warp allocates TMEM and writes the base address to shared memory
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c.base + OFF_BAR + 8),
+                         "n"(TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        fence_async_smem();  // weights (generic-proxy stores) become visible to the tensor core (async proxy)
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        c.tmem = *reinterpret_cast<const volatile uint32_t *>(reinterpret_cast<const unsigned char *>(c.gen) + OFF_BAR + 8);
+    }
+
+    SRE_DEV static void teardown(Ctx &c) {
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x < 32)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(c.tmem), "n"(TMEM_COLS) : "memory");
+    }
+
+    // CTA-cooperative: EVERY thread of the CTA calls this each step (convergent).  x = observation of the thread's
+    // own environment.  `active` is OR-reduced over the CTA by the barrier that hands the A tile to the tensor core;
+    // the result lets the caller leave its loop CTA-uniformly.
+    SRE_DEV static bool forward(Ctx &c, const float *x, float *out, bool active) {
+        const int r = threadIdx.x;
+        const float *sm = c.gen;
+        // ---- layer 1 + tanh + hi/lo split, 16 outputs at a time -> this thread's row of A_hi / A_lo ----
+#pragma unroll 1
+        for (int j0 = 0; j0 < HID; j0 += 16) {
+            float a[16];
+            const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B1 / 4 + j0);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 b = bv[q];
+                a[4 * q] = b.x; a[4 * q + 1] = b.y; a[4 * q + 2] = b.z; a[4 * q + 3] = b.w;
+            }
+#pragma unroll
+            for (int i = 0; i < IN; i++) {
+                const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W1T / 4 + i * HID + j0);
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const float4 w = wv[q];
+                    a[4 * q] = fmaf(w.x, x[i], a[4 * q]);
+                    a[4 * q + 1] = fmaf(w.y, x[i], a[4 * q + 1]);
+                    a[4 * q + 2] = fmaf(w.z, x[i], a[4 * q + 2]);
+                    a[4 * q + 3] = fmaf(w.w, x[i], a[4 * q + 3]);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                float h[4], hi[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    h[e] = tanh_prescaled(a[4 * q + e]);
+                    hi[e] = __uint_as_float(tf32_hi(h[e]));
+                }
+                const uint32_t off = sw_off(r, j0 + 4 * q, A_KB);
+                st_shared_v4(c.base + OFF_A_HI + off, hi[0], hi[1], hi[2], hi[3]);
+                if (!SINGLE_PASS)
+                    st_shared_v4(c.base + OFF_A_LO + off, h[0] - hi[0], h[1] - hi[1], h[2] - hi[2], h[3] - hi[3]);
+            }
+        }
+        // ---- hand the tile to the tensor core ----
+        fence_async_smem();
+        tc_fence_before();
+        const bool any = __syncthreads_or(active);
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            uint32_t acc = 0;
+#pragma unroll
+            for (int pass = SINGLE_PASS ? 2 : 0; pass < 3; pass++) {
+                const uint32_t a0 = c.base + (pass == 0 ? OFF_A_LO : OFF_A_HI);
+                const uint32_t b0 = c.base + (pass == 1 ? OFF_B_LO : OFF_B_HI);
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {  // K = 64 in slices of 8 tf32 (32 bytes inside the 128-byte atom)
+                    const uint32_t ao = (ks >> 2) * A_KB + (ks & 3) * 32, bo = (ks >> 2) * B_KB + (ks & 3) * 32;
+                    umma_tf32(c.tmem, umma_desc_k_sw128(a0 + ao), umma_desc_k_sw128(b0 + bo), UMMA_IDESC_TF32_M128_N64, acc);
+                    acc = 1;
+                }
+            }
+            umma_commit(c.base + OFF_BAR);
+        }
+        mbar_wait(c.base + OFF_BAR, c.parity);
+        c.parity ^= 1;
+        tc_fence_after();
+        // ---- epilogue: this thread's row of D -> + b2, tanh, layer 3 ----
+        float o[OUT];
+#pragma unroll
+        for (int q = 0; q < OUT; q++) o[q] = sm[OFF_B3 / 4 + q];
+        const uint32_t trow = c.tmem + ((uint32_t)(r & ~31) << 16);  // warp w reads lanes 32w .. 32w + 31
+#pragma unroll
+        for (int j0 = 0; j0 < HID; j0 += 16) {
+            float d[16];
+            tmem_ld16(trow + j0, d);
+            tmem_ld_wait();
+            const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B2 / 4 + j0);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 b = bv[q];
+                d[4 * q] = tanh_prescaled(d[4 * q] + b.x);
+                d[4 * q + 1] = tanh_prescaled(d[4 * q + 1] + b.y);
+                d[4 * q + 2] = tanh_prescaled(d[4 * q + 2] + b.z);
+                d[4 * q + 3] = tanh_prescaled(d[4 * q + 3] + b.w);
+            }
+#pragma unroll
+            for (int oo = 0; oo < OUT; oo++) {
+                const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W3 / 4 + oo * HID + j0);
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const float4 w = wv[q];
+                    o[oo] = fmaf(w.x, d[4 * q], o[oo]);
+                    o[oo] = fmaf(w.y, d[4 * q + 1], o[oo]);
+                    o[oo] = fmaf(w.z, d[4 * q + 2], o[oo]);
+                    o[oo] = fmaf(w.w, d[4 * q + 3], o[oo]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < OUT; q++) out[q] = o[q];
+        tc_fence_before();  // the next step's MMA overwrites the accumulators: order our TMEM reads before its barrier
+        return any;
+    }
+};
+
+}  // namespace sre

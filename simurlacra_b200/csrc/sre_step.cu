@@ -352,8 +352,16 @@ int step_rew_dispatch(const sre_env_cfg *cfg, const void *params, const void *st
                                  : step_rew_t<float>(cfg, params, state, act, rew, n, s);
 }
 
+bool policy_is_tc_shape(const KPolicy &kp, int n_obs, int n_act);
+int policy_forward_tc_dispatch(const KPolicy &kp, const float *obs, int n_obs, float *act, int n_act, long long n,
+                               cudaStream_t s);
+
 int policy_forward_dispatch(const KPolicy &kp, const float *obs, int n_obs, float *act, int n_act, long long n,
                             cudaStream_t s) {
+    if (policy_is_tc_shape(kp, n_obs, n_act)) {
+        const int r = policy_forward_tc_dispatch(kp, obs, n_obs, act, n_act, n, s);
+        if (r != -1000) return r;
+    }
     policy_forward_kernel<<<nblocks(n, 128), 128, 0, s>>>(kp, obs, n_obs, act, n_act, n);
     return (int)cudaGetLastError();
 }

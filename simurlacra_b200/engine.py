@@ -132,7 +132,7 @@ def make_distr_table(entries: Sequence[dict]):
 
 
 def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), feats=(), hidden_nonlin: int = 0,
-                output_nonlin: int = 0, cartpole_feats: bool = False) -> L.Policy:
+                output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = 0) -> L.Policy:
     p = L.Policy()
     p.kind = kind
     p.n_layers = max(len(sizes) - 1, 0)
@@ -142,6 +142,7 @@ def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), fea
     for i, f in enumerate(feats):
         p.feats[i] = L.FEATS[f] if isinstance(f, str) else int(f)
     p.hidden_nonlin, p.output_nonlin, p.cartpole_feats = hidden_nonlin, output_nonlin, int(cartpole_feats)
+    p.precision = int(precision)
     if weights is not None:
         if not (weights.is_cuda and weights.dtype == torch.float32 and weights.is_contiguous()):
             raise ValueError("policy weights must be a contiguous float32 CUDA tensor")
