@@ -178,6 +178,7 @@ def main():
     ap.add_argument("--horizon", type=int, default=600)
     ap.add_argument("--hidden", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", type=int, default=0, help="0 fp32 FMA, 1 tcgen05 3xTF32, 2 tcgen05 TF32")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
@@ -204,7 +205,7 @@ def main():
     w_dev = w_host.to(dev)
     cfg = E.make_cfg(L.QQ, 1 / 250.0, H, dtype=torch.float32, act_norm=True)
     distr = E.make_distr_table(qq_randomizer(E.nominal_params(L.QQ)))
-    pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes)
+    pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes, precision=args.precision)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def barrier():

@@ -7,6 +7,7 @@
 #pragma once
 #include "sre_core.cuh"
 #include "sre_policy.cuh"
+#include "sre_policy_tc.cuh"
 
 namespace sre {
 
@@ -17,6 +18,8 @@ namespace sre {
 #define SRE_PV_FNN16 16
 #define SRE_PV_FNN32 32
 #define SRE_PV_FNN64 64
+#define SRE_PV_TC 1000    // [do,64,64,da] tanh, hidden layer on the tensor cores, 3 x TF32 (sre_policy_tc.cuh)
+#define SRE_PV_TC1 1001   // the same, single TF32 pass
 
 struct KIO {
     long long n_envs, n_rows;
@@ -81,8 +84,9 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
 
 // CTA shape per variant: the tiled FNN production build runs 256-thread CTAs, two per SM (16 warps, 128 registers)
 template <typename R, int PV> struct LaunchShape {
-    static constexpr int THREADS = (PV >= 16 && sizeof(R) == 4) ? 256 : 128;
-    static constexpr int MIN_BLOCKS = (PV >= 16 && sizeof(R) == 4) ? 2 : 1;
+    static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile, two CTAs per SM (99 KB smem each)
+    static constexpr int THREADS = TC ? 128 : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128);
+    static constexpr int MIN_BLOCKS = TC ? 2 : ((PV >= 16 && sizeof(R) == 4) ? 2 : 1);
 };
 
 template <int KIND, typename R, int PV>
@@ -93,7 +97,10 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     using RC = Rec<KIND, R>;
     constexpr int DS = E::DS, DO = E::DO, DA = E::DA, DP = E::DP, NH = E::NH, W = RC::W;
     // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
-    using Fast = FnnTiled<DO, (PV >= 16 ? PV : 16), DA, sizeof(R) == 4>;
+    using Fast = FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>;
+    constexpr bool TC = PV >= SRE_PV_TC;
+    using Tc = FnnTC<DO, DA, PV == SRE_PV_TC1>;
+    typename Tc::Ctx tc;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *sm_w = reinterpret_cast<float *>(smem_raw);
@@ -101,7 +108,9 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
     float *h1s = sm_w + Fast::W_FLOATS + warp * Fast::H1S_FLOATS;  // only meaningful for the tiled FNN variants
 
-    if (PV >= 16) Fast::stage(pol.weights, sm_w);
+    if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) + (size_t)(blockDim.x / 32) * 32 * W * sizeof(R),
+                      pol.weights);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
+    else if (PV >= 16) Fast::stage(pol.weights, sm_w);
     else if (PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) stage_generic(pol, sm_w);
     __syncthreads();
 
@@ -211,7 +220,11 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             float of[DO], af[DA];
 #pragma unroll
             for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
-            if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
+            if (TC) {
+                // CTA-cooperative (tcgen05): its barrier also tells whether any lane of the CTA is still running
+                const bool any = Tc::forward(tc, of, af, lane_state != IDLE);
+                if (!any && !record && !io.row_flag) break;  // CTA-uniform exit
+            } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
             else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
             else linear_forward<DO, DA>(pol, sm_w, of, af);
 #pragma unroll
@@ -282,12 +295,13 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             __syncwarp();
         }
         if (io.row_flag && valid) io.row_flag[row * N + n] = flag;
-        if (!record && !io.row_flag) {
+        if (!TC && !record && !io.row_flag) {
             // early exit accounting: the warp leaves when every lane is idle
             if (__ballot_sync(0xffffffffu, lane_state != IDLE) == 0u) break;
         }
     }
     if (valid && io.status) io.status[n] = status;
+    if (TC) Tc::teardown(tc);
 
     // ---- statistics: one atomic set per CTA ----
     if (io.stats) {
@@ -312,7 +326,8 @@ static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPol
     constexpr int W = Rec<KIND, R>::W;
     const int threads = LaunchShape<R, PV>::THREADS;
     const long long blocks = (io.n_envs + threads - 1) / threads;
-    const size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
+    size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
+    if (PV >= SRE_PV_TC) smem += FnnTC<Env<KIND, R>::DO, Env<KIND, R>::DA>::SMEM_BYTES;
     auto kern = rollout_kernel<KIND, R, PV>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -335,6 +350,11 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
     const bool two_hidden = pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
+    if (two_hidden && pol.sizes[1] == 64 && pol.precision != SRE_PREC_FP32 && sizeof(R) == 4) {
+        pol.smem_floats = 0;
+        return pol.precision == SRE_PREC_TF32 ? launch_rollout_pv<KIND, R, SRE_PV_TC1>(cfg, distr, pol, io, stream)
+                                              : launch_rollout_pv<KIND, R, SRE_PV_TC>(cfg, distr, pol, io, stream);
+    }
     if (two_hidden && pol.sizes[1] == 64) {
         pol.smem_floats = FnnTiled<E::DO, 64, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
         return launch_rollout_pv<KIND, R, SRE_PV_FNN64>(cfg, distr, pol, io, stream);

@@ -60,3 +60,68 @@ def test_policy_forward_tensor_core_matches_fp32(E, n_obs, n_act, n):
     assert err[L.PREC_TF32X3] < 5e-6, err        # the split reaches the accuracy of the fp32 FMA kernel
     assert err[L.PREC_TF32] < 2e-2, err          # single pass: TF32 accuracy
     assert err[L.PREC_TF32] > err[L.PREC_TF32X3]  # ... and it really is a different arithmetic
+
+
+def _qq_distr(E):
+    from simurlacra_b200 import _lib as L
+
+    names = ["gravity_const", "motor_resistance", "motor_back_emf", "mass_rot_pole", "length_rot_pole",
+             "damping_rot_pole", "mass_pend_pole", "length_pend_pole", "damping_pend_pole"]
+    nom = E.nominal_params(L.QQ)
+    div = dict(gravity_const=10, damping_rot_pole=4, damping_pend_pole=4)
+    clip = dict(gravity_const=1e-3, motor_resistance=1e-3, damping_rot_pole=1e-9, damping_pend_pole=1e-9)
+    return E.make_distr_table([dict(param_index=i, kind="normal", a=nom[i], b=nom[i] / div.get(k, 5),
+                                    clip_lo=clip.get(k, 1e-4)) for i, k in enumerate(names)])
+
+
+@pytest.mark.parametrize("kind_name,n_obs,n_act", [("qq-su", 6, 1), ("qbb", 8, 2), ("qcp-su", 5, 1)])
+@pytest.mark.parametrize("n_envs", [1, 130, 1000])
+def test_rollout_tensor_core_tracks_fp32_rollout(E, kind_name, n_obs, n_act, n_envs):
+    """Same seeds, same weights: the tensor-core rollout follows the fp32-FMA rollout (identical DR draws and initial
+    states; trajectories agree to fp32 noise over a short horizon; same rows written, same flags)."""
+    from simurlacra_b200 import _lib as L
+
+    kind = E.KIND_BY_NAME[kind_name]
+    sizes = [n_obs, 64, 64, n_act]
+    wd = torch.from_numpy(_weights(sizes, seed=3, scale=0.2)).to(DEV)
+    H = 40
+    cfg = E.make_cfg(kind, 1 / 250.0 if kind_name != "qbb" else 0.01, H, dtype=torch.float32, act_norm=True, long_pole=True)
+    distr = _qq_distr(E) if kind_name == "qq-su" else None
+    res = {}
+    for prec in (L.PREC_FP32, L.PREC_TF32X3):
+        pol = E.make_policy(L.POL_FNN, wd, sizes=sizes, precision=prec)
+        res[prec] = E.rollout(cfg, pol, n_envs, H + 1, device=DEV, distr=distr, seed=11, record=True)
+    a, b = res[L.PREC_FP32], res[L.PREC_TF32X3]
+    torch.testing.assert_close(a["params"], b["params"], rtol=0, atol=0)
+    torch.testing.assert_close(a["state"][0], b["state"][0], rtol=0, atol=0)
+    torch.testing.assert_close(a["act"][0], b["act"][0], rtol=1e-4, atol=1e-5)
+    same_len = (a["length"] == b["length"]).float().mean()
+    assert float(same_len) > 0.98
+    m = (a["length"] == b["length"]) & (a["length"] >= 10)
+    if int(m.sum()):
+        torch.testing.assert_close(a["state"][10][m], b["state"][10][m], rtol=2e-3, atol=2e-3)
+        torch.testing.assert_close(a["ret"][m], b["ret"][m], rtol=2e-3, atol=2e-3)
+    assert int(b["status"].abs().sum()) == 0
+
+
+def test_rollout_tensor_core_auto_reset_statistics(E):
+    from simurlacra_b200 import _lib as L
+
+    sizes = [6, 64, 64, 1]
+    wd = torch.from_numpy(_weights(sizes, seed=0)).to(DEV)
+    N, H = 20000, 120
+    cfg = E.make_cfg(L.QQ, 1 / 250.0, H, dtype=torch.float32, act_norm=True)
+    out = {}
+    for prec in (L.PREC_FP32, L.PREC_TF32X3, L.PREC_TF32):
+        pol = E.make_policy(L.POL_FNN, wd, sizes=sizes, precision=prec)
+        r = E.rollout(cfg, pol, N, H + 1, device=DEV, distr=_qq_distr(E), seed=1, auto_reset=True, record=False)
+        out[prec] = r["stats"].cpu().numpy()
+    for prec in (L.PREC_TF32X3, L.PREC_TF32):
+        assert abs(out[prec][L.STAT_STEPS] - out[L.PREC_FP32][L.STAT_STEPS]) <= 0.01 * N * H
+        mean_ret = out[prec][L.STAT_SUM_RET] / out[prec][L.STAT_EPISODES]
+        ref_ret = out[L.PREC_FP32][L.STAT_SUM_RET] / out[L.PREC_FP32][L.STAT_EPISODES]
+        assert abs(mean_ret - ref_ret) < 0.02 * abs(ref_ret) + 1e-3
+    # early exit without auto-reset: every lane finishes, the CTA-wide exit must not hang
+    pol = E.make_policy(L.POL_FNN, wd, sizes=sizes, precision=L.PREC_TF32X3)
+    r = E.rollout(cfg, pol, 777, H + 1, device=DEV, distr=_qq_distr(E), seed=2, record=False)
+    assert int(r["length"].min()) >= 1 and int(r["length"].max()) <= H
