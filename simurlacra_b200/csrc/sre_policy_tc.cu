@@ -8,7 +8,7 @@ namespace sre {
 template <int IN, int OUT, bool SP>
 __global__ void __launch_bounds__(128) policy_forward_tc_kernel(const __grid_constant__ KPolicy pol, const float *obs,
                                                                 float *act, long long N) {
-    using F = FnnTC<IN, OUT, SP>;
+    using F = FnnTC2<IN, OUT, SP>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     typename F::Ctx c;
     F::setup(c, smem_raw, pol.weights);
@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(128) policy_forward_tc_kernel(const __grid_con
 
 template <int IN, int OUT, bool SP>
 static int launch_pf(const KPolicy &kp, const float *obs, float *act, long long n, cudaStream_t s) {
-    using F = FnnTC<IN, OUT, SP>;
+    using F = FnnTC2<IN, OUT, SP>;
     auto kern = policy_forward_tc_kernel<IN, OUT, SP>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F::SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;

@@ -261,4 +261,223 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC {
     }
 };
 
+
+// ---- variant 2: A operand in TENSOR MEMORY, K split in two halves ---------------------------------------------
+// The shared-memory A tiles above cost 64 KB per CTA (two CTAs per SM = 8 warps: latency bound, profiles/r01_d).
+// Here the activations never touch shared memory: every thread writes its row of h1 (hi and lo parts) straight into
+// TMEM with tcgen05.st and the MMA reads A from TMEM (tcgen05.mma [d], [a], b_desc).  To keep a tile at 128 TMEM
+// columns (D 64 + A_hi 32 + A_lo 32 -> four tiles per SM) the hidden layer is fed in two K halves of 32 units:
+//   half 0: L1 + tanh + split of units 0..31 -> tcgen05.st -> barrier -> 12 MMAs (lo*hi, hi*lo, hi*hi; 4 K slices)
+//   half 1: the same for units 32..63; its L1 / tanh arithmetic overlaps the MMAs of half 0, only the tcgen05.st
+//           waits (mbarrier) until they have consumed the A columns
+// Shared memory per CTA: W2 hi/lo (32 KB, canonical K-major SWIZZLE_128B) + W1/b1/b2/W3/b3 (2.3 KB).
+SRE_DEV void tmem_st16(uint32_t taddr, const uint32_t *r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+SRE_DEV void tmem_st8(uint32_t taddr, const uint32_t *r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
+                 "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+SRE_DEV void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+SRE_DEV void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
+    static constexpr int HID = 64;
+    static constexpr int THREADS = 128;
+    static constexpr int TMEM_COLS = 128;  // D [0,64), A_hi [64,96), A_lo [96,128)
+    static constexpr int B_KB = 64 * 128;
+    static constexpr int OFF_B_HI = 0;
+    static constexpr int OFF_B_LO = OFF_B_HI + 2 * B_KB;
+    static constexpr int OFF_W1T = OFF_B_LO + 2 * B_KB;
+    static constexpr int OFF_B1 = OFF_W1T + IN * HID * 4;
+    static constexpr int OFF_B2 = OFF_B1 + HID * 4;
+    static constexpr int OFF_W3 = OFF_B2 + HID * 4;
+    static constexpr int OFF_B3 = OFF_W3 + OUT * HID * 4;
+    static constexpr int OFF_BAR = OFF_B3 + 16;             // two mbarriers (16 B) + TMEM base address (4 B)
+    static constexpr int SMEM_BYTES = OFF_BAR + 32 + 1024;  // + slack for the manual 1024-byte alignment
+    static constexpr float PRE = SRE_TANH_PRESCALE;
+
+    struct Ctx {
+        uint32_t base, tmem, parity;
+        const float *gen;
+    };
+
+    SRE_DEV static uint32_t tf32_hi(float x) { return __float_as_uint(x) & 0xFFFFE000u; }
+    SRE_DEV static uint32_t sw_off(int row, int k, int kb_bytes) {
+        return (uint32_t)((k >> 5) * kb_bytes + row * 128 + ((((k & 31) >> 2) ^ (row & 7)) << 4) + ((k & 3) << 2));
+    }
+
+    SRE_DEV static void setup(Ctx &c, unsigned char *smem_raw, const float *__restrict__ w) {
+        const uint32_t raw = smem_u32(smem_raw);
+        const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
+        c.base = raw + pad;
+        c.gen = reinterpret_cast<const float *>(smem_raw + pad);
+        c.parity = 0;
+        float *g = const_cast<float *>(c.gen);
+        const float *W1 = w, *b1 = W1 + IN * HID, *W2 = b1 + HID, *b2 = W2 + HID * HID, *W3 = b2 + HID,
+                    *b3 = W3 + OUT * HID;
+        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) g[OFF_W1T / 4 + (i % IN) * HID + i / IN] = PRE * W1[i];
+        for (int i = threadIdx.x; i < HID; i += blockDim.x) {
+            g[OFF_B1 / 4 + i] = PRE * b1[i];
+            g[OFF_B2 / 4 + i] = PRE * b2[i];
+        }
+        for (int i = threadIdx.x; i < OUT * HID; i += blockDim.x) g[OFF_W3 / 4 + i] = W3[i];
+        for (int i = threadIdx.x; i < 4; i += blockDim.x) g[OFF_B3 / 4 + i] = i < OUT ? b3[i] : 0.f;
+        for (int i = threadIdx.x; i < HID * HID; i += blockDim.x) {
+            const int n = i / HID, k = i % HID;
+            const float v = PRE * W2[i];
+            const float hi = __uint_as_float(tf32_hi(v));
+            const uint32_t off = sw_off(n, k, B_KB);
+            g[(OFF_B_HI + off) / 4] = hi;
+            g[(OFF_B_LO + off) / 4] = v - hi;
+        }
+        if (threadIdx.x == 0) {
+            mbar_init(c.base + OFF_BAR, 1);
+            mbar_init(c.base + OFF_BAR + 8, 1);
+        }
+        if (threadIdx.x < 32) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c.base + OFF_BAR + 16),
+                         "n"(TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        fence_async_smem();
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        c.tmem = *reinterpret_cast<const volatile uint32_t *>(reinterpret_cast<const unsigned char *>(c.gen) + OFF_BAR + 16);
+    }
+
+    SRE_DEV static void teardown(Ctx &c) {
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x < 32)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(c.tmem), "n"(TMEM_COLS) : "memory");
+    }
+
+    // layer 1 pre-activations of 16 hidden units j0 .. j0 + 15 of this thread's environment
+    SRE_DEV static void l1_chunk(const float *sm, const float *x, int j0, float *a) {
+        const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B1 / 4 + j0);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float4 b = bv[q];
+            a[4 * q] = b.x; a[4 * q + 1] = b.y; a[4 * q + 2] = b.z; a[4 * q + 3] = b.w;
+        }
+#pragma unroll
+        for (int i = 0; i < IN; i++) {
+            const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W1T / 4 + i * HID + j0);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 w = wv[q];
+                a[4 * q] = fmaf(w.x, x[i], a[4 * q]);
+                a[4 * q + 1] = fmaf(w.y, x[i], a[4 * q + 1]);
+                a[4 * q + 2] = fmaf(w.z, x[i], a[4 * q + 2]);
+                a[4 * q + 3] = fmaf(w.w, x[i], a[4 * q + 3]);
+            }
+        }
+    }
+    // tanh + hi/lo split of 8 pre-activations -> this thread's TMEM lane, columns col .. col + 7 of A_hi / A_lo
+    SRE_DEV static void act_store8(const float *a, uint32_t t_hi, uint32_t t_lo) {
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const float h = tanh_prescaled(a[e]);
+            hi[e] = tf32_hi(h);
+            lo[e] = __float_as_uint(h - __uint_as_float(hi[e]));
+        }
+        tmem_st8(t_hi, hi);
+        if (!SINGLE_PASS) tmem_st8(t_lo, lo);
+    }
+
+    SRE_DEV static bool forward(Ctx &c, const float *x, float *out, bool active) {
+        const int r = threadIdx.x;
+        const float *sm = c.gen;
+        const uint32_t lane_base = (uint32_t)(r & ~31) << 16;
+        const uint32_t t_d = c.tmem, t_ahi = c.tmem + 64, t_alo = c.tmem + 96;
+        bool any = false;
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+#pragma unroll
+            for (int ch = 0; ch < 2; ch++) {
+                float a[16];
+                l1_chunk(sm, x, half * 32 + ch * 16, a);
+                if (half == 1 && ch == 0) {  // the MMAs of half 0 must have consumed the A columns
+                    mbar_wait(c.base + OFF_BAR, c.parity);
+                    tc_fence_after();
+                }
+                act_store8(a, lane_base + t_ahi + ch * 16, lane_base + t_alo + ch * 16);
+                act_store8(a + 8, lane_base + t_ahi + ch * 16 + 8, lane_base + t_alo + ch * 16 + 8);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            if (half == 0) any = __syncthreads_or(active);
+            else __syncthreads();
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+                uint32_t acc = half;
+#pragma unroll
+                for (int pass = SINGLE_PASS ? 2 : 0; pass < 3; pass++) {
+                    const uint32_t a0 = pass == 0 ? t_alo : t_ahi;
+                    const uint32_t b0 = c.base + (pass == 1 ? OFF_B_LO : OFF_B_HI) + half * B_KB;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) {
+                        umma_tf32_ts(t_d, a0 + ks * 8, umma_desc_k_sw128(b0 + ks * 32), UMMA_IDESC_TF32_M128_N64, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit(c.base + OFF_BAR + half * 8);
+            }
+        }
+        mbar_wait(c.base + OFF_BAR + 8, c.parity);
+        c.parity ^= 1;
+        tc_fence_after();
+        float o[OUT];
+#pragma unroll
+        for (int q = 0; q < OUT; q++) o[q] = sm[OFF_B3 / 4 + q];
+#pragma unroll
+        for (int j0 = 0; j0 < HID; j0 += 16) {
+            float d[16];
+            tmem_ld16(lane_base + t_d + j0, d);
+            tmem_ld_wait();
+            const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B2 / 4 + j0);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 b = bv[q];
+                d[4 * q] = tanh_prescaled(d[4 * q] + b.x);
+                d[4 * q + 1] = tanh_prescaled(d[4 * q + 1] + b.y);
+                d[4 * q + 2] = tanh_prescaled(d[4 * q + 2] + b.z);
+                d[4 * q + 3] = tanh_prescaled(d[4 * q + 3] + b.w);
+            }
+#pragma unroll
+            for (int oo = 0; oo < OUT; oo++) {
+                const float4 *wv = reinterpret_cast<const float4 *>(sm + OFF_W3 / 4 + oo * HID + j0);
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const float4 w = wv[q];
+                    o[oo] = fmaf(w.x, d[4 * q], o[oo]);
+                    o[oo] = fmaf(w.y, d[4 * q + 1], o[oo]);
+                    o[oo] = fmaf(w.z, d[4 * q + 2], o[oo]);
+                    o[oo] = fmaf(w.w, d[4 * q + 3], o[oo]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < OUT; q++) out[q] = o[q];
+        tc_fence_before();
+        return any;
+    }
+};
+
 }  // namespace sre

@@ -83,10 +83,13 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
 }
 
 // CTA shape per variant: the tiled FNN production build runs 256-thread CTAs, two per SM (16 warps, 128 registers)
+#ifndef SRE_TC_BLOCKS
+#define SRE_TC_BLOCKS 4  // resident CTAs (= UMMA tiles) per SM of the tensor-core variant: 128 TMEM columns each
+#endif
 template <typename R, int PV> struct LaunchShape {
-    static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile, two CTAs per SM (99 KB smem each)
+    static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile
     static constexpr int THREADS = TC ? 128 : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128);
-    static constexpr int MIN_BLOCKS = TC ? 2 : ((PV >= 16 && sizeof(R) == 4) ? 2 : 1);
+    static constexpr int MIN_BLOCKS = TC ? SRE_TC_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? 2 : 1);
 };
 
 template <int KIND, typename R, int PV>
@@ -99,7 +102,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
     using Fast = FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>;
     constexpr bool TC = PV >= SRE_PV_TC;
-    using Tc = FnnTC<DO, DA, PV == SRE_PV_TC1>;
+    using Tc = FnnTC2<DO, DA, PV == SRE_PV_TC1>;
     typename Tc::Ctx tc;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -108,8 +111,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
     float *h1s = sm_w + Fast::W_FLOATS + warp * Fast::H1S_FLOATS;  // only meaningful for the tiled FNN variants
 
-    if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) + (size_t)(blockDim.x / 32) * 32 * W * sizeof(R),
-                      pol.weights);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
+    if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) +
+                              (io.traj ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0), pol.weights);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
     else if (PV >= 16) Fast::stage(pol.weights, sm_w);
     else if (PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) stage_generic(pol, sm_w);
     __syncthreads();
@@ -327,7 +330,8 @@ static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPol
     const int threads = LaunchShape<R, PV>::THREADS;
     const long long blocks = (io.n_envs + threads - 1) / threads;
     size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
-    if (PV >= SRE_PV_TC) smem += FnnTC<Env<KIND, R>::DO, Env<KIND, R>::DA>::SMEM_BYTES;
+    if (PV >= SRE_PV_TC && !io.traj) smem = 0;  // the staging area is only needed when records are written
+    if (PV >= SRE_PV_TC) smem += FnnTC2<Env<KIND, R>::DO, Env<KIND, R>::DA>::SMEM_BYTES;
     auto kern = rollout_kernel<KIND, R, PV>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
