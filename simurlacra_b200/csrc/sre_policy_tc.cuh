@@ -19,6 +19,25 @@ namespace sre {
 
 SRE_DEV uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// packed FP32 pairs (Blackwell add/mul/fma .f32x2: two lanes per issue slot)
+SRE_DEV unsigned long long add2(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// tanh of a packed pair of prescaled arguments (see tanh_prescaled): 2 MUFU.EX2, 1 packed add, 2 MUFU.RCP, 1 packed fma
+SRE_DEV unsigned long long tanh2_prescaled(unsigned long long zs) {
+    float z0, z1, t0, t1, r0, r1;
+    unpack2(zs, z0, z1);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(z0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(z1));
+    float a0, a1;
+    unpack2(add2(pack2(t0, t1), pack2(1.0f, 1.0f)), a0, a1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(a0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(a1));
+    return fma2(pack2(r0, r1), pack2(-2.0f, -2.0f), pack2(1.0f, 1.0f));
+}
+
 SRE_DEV void st_shared_v4(uint32_t addr, float a, float b, float c, float d) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -367,13 +386,14 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
             asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(c.tmem), "n"(TMEM_COLS) : "memory");
     }
 
-    // layer 1 pre-activations of 16 hidden units j0 .. j0 + 15 of this thread's environment
-    SRE_DEV static void l1_chunk(const float *sm, const float *x, int j0, float *a) {
+    // layer 1 pre-activations of 16 hidden units j0 .. j0 + 15 as 8 packed pairs; x2[i] = {x_i, x_i}
+    SRE_DEV static void l1_chunk(const float *sm, const unsigned long long *x2, int j0, unsigned long long *a2) {
         const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B1 / 4 + j0);
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             const float4 b = bv[q];
-            a[4 * q] = b.x; a[4 * q + 1] = b.y; a[4 * q + 2] = b.z; a[4 * q + 3] = b.w;
+            a2[2 * q] = pack2(b.x, b.y);
+            a2[2 * q + 1] = pack2(b.z, b.w);
         }
 #pragma unroll
         for (int i = 0; i < IN; i++) {
@@ -381,21 +401,21 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const float4 w = wv[q];
-                a[4 * q] = fmaf(w.x, x[i], a[4 * q]);
-                a[4 * q + 1] = fmaf(w.y, x[i], a[4 * q + 1]);
-                a[4 * q + 2] = fmaf(w.z, x[i], a[4 * q + 2]);
-                a[4 * q + 3] = fmaf(w.w, x[i], a[4 * q + 3]);
+                a2[2 * q] = fma2(pack2(w.x, w.y), x2[i], a2[2 * q]);
+                a2[2 * q + 1] = fma2(pack2(w.z, w.w), x2[i], a2[2 * q + 1]);
             }
         }
     }
-    // tanh + hi/lo split of 8 pre-activations -> this thread's TMEM lane, columns col .. col + 7 of A_hi / A_lo
-    SRE_DEV static void act_store8(const float *a, uint32_t t_hi, uint32_t t_lo) {
+    // tanh + hi/lo split of 4 packed pairs -> this thread's TMEM lane, 8 columns of A_hi / A_lo
+    SRE_DEV static void act_store8(const unsigned long long *a2, uint32_t t_hi, uint32_t t_lo) {
         uint32_t hi[8], lo[8];
 #pragma unroll
-        for (int e = 0; e < 8; e++) {
-            const float h = tanh_prescaled(a[e]);
-            hi[e] = tf32_hi(h);
-            lo[e] = __float_as_uint(h - __uint_as_float(hi[e]));
+        for (int e = 0; e < 4; e++) {
+            const unsigned long long h = tanh2_prescaled(a2[e]);
+            const unsigned long long hh = h & 0xFFFFE000FFFFE000ull;
+            const unsigned long long ll = fma2(hh, pack2(-1.0f, -1.0f), h);  // h - hi, exact
+            hi[2 * e] = (uint32_t)hh; hi[2 * e + 1] = (uint32_t)(hh >> 32);
+            lo[2 * e] = (uint32_t)ll; lo[2 * e + 1] = (uint32_t)(ll >> 32);
         }
         tmem_st8(t_hi, hi);
         if (!SINGLE_PASS) tmem_st8(t_lo, lo);
@@ -407,18 +427,21 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
         const uint32_t lane_base = (uint32_t)(r & ~31) << 16;
         const uint32_t t_d = c.tmem, t_ahi = c.tmem + 64, t_alo = c.tmem + 96;
         bool any = false;
+        unsigned long long x2[IN];
 #pragma unroll
-        for (int half = 0; half < 2; half++) {
-#pragma unroll
+        for (int i = 0; i < IN; i++) x2[i] = pack2(x[i], x[i]);
+#pragma unroll 1
+        for (int half = 0; half < 2; half++) {  // not unrolled: the hot loop has to stay inside the instruction cache
+#pragma unroll 1
             for (int ch = 0; ch < 2; ch++) {
-                float a[16];
-                l1_chunk(sm, x, half * 32 + ch * 16, a);
+                unsigned long long a[8];
+                l1_chunk(sm, x2, half * 32 + ch * 16, a);
                 if (half == 1 && ch == 0) {  // the MMAs of half 0 must have consumed the A columns
                     mbar_wait(c.base + OFF_BAR, c.parity);
                     tc_fence_after();
                 }
                 act_store8(a, lane_base + t_ahi + ch * 16, lane_base + t_alo + ch * 16);
-                act_store8(a + 8, lane_base + t_ahi + ch * 16 + 8, lane_base + t_alo + ch * 16 + 8);
+                act_store8(a + 4, lane_base + t_ahi + ch * 16 + 8, lane_base + t_alo + ch * 16 + 8);
             }
             tmem_st_wait();
             tc_fence_before();
@@ -443,22 +466,21 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
         mbar_wait(c.base + OFF_BAR + 8, c.parity);
         c.parity ^= 1;
         tc_fence_after();
-        float o[OUT];
+        unsigned long long o2[OUT];
 #pragma unroll
-        for (int q = 0; q < OUT; q++) o[q] = sm[OFF_B3 / 4 + q];
-#pragma unroll
+        for (int q = 0; q < OUT; q++) o2[q] = pack2(sm[OFF_B3 / 4 + q], 0.0f);
+#pragma unroll 1
         for (int j0 = 0; j0 < HID; j0 += 16) {
             float d[16];
             tmem_ld16(lane_base + t_d + j0, d);
             tmem_ld_wait();
+            unsigned long long h2[8];
             const float4 *bv = reinterpret_cast<const float4 *>(sm + OFF_B2 / 4 + j0);
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const float4 b = bv[q];
-                d[4 * q] = tanh_prescaled(d[4 * q] + b.x);
-                d[4 * q + 1] = tanh_prescaled(d[4 * q + 1] + b.y);
-                d[4 * q + 2] = tanh_prescaled(d[4 * q + 2] + b.z);
-                d[4 * q + 3] = tanh_prescaled(d[4 * q + 3] + b.w);
+                h2[2 * q] = tanh2_prescaled(add2(pack2(d[4 * q], d[4 * q + 1]), pack2(b.x, b.y)));
+                h2[2 * q + 1] = tanh2_prescaled(add2(pack2(d[4 * q + 2], d[4 * q + 3]), pack2(b.z, b.w)));
             }
 #pragma unroll
             for (int oo = 0; oo < OUT; oo++) {
@@ -466,15 +488,17 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
                     const float4 w = wv[q];
-                    o[oo] = fmaf(w.x, d[4 * q], o[oo]);
-                    o[oo] = fmaf(w.y, d[4 * q + 1], o[oo]);
-                    o[oo] = fmaf(w.z, d[4 * q + 2], o[oo]);
-                    o[oo] = fmaf(w.w, d[4 * q + 3], o[oo]);
+                    o2[oo] = fma2(pack2(w.x, w.y), h2[2 * q], o2[oo]);
+                    o2[oo] = fma2(pack2(w.z, w.w), h2[2 * q + 1], o2[oo]);
                 }
             }
         }
 #pragma unroll
-        for (int q = 0; q < OUT; q++) out[q] = o[q];
+        for (int q = 0; q < OUT; q++) {
+            float e, od;
+            unpack2(o2[q], e, od);
+            out[q] = e + od;
+        }
         tc_fence_before();
         return any;
     }
