@@ -25,17 +25,34 @@ SRE_DEV unsigned long long add2(unsigned long long a, unsigned long long b) {
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
     return d;
 }
-// tanh of a packed pair of prescaled arguments (see tanh_prescaled): 2 MUFU.EX2, 1 packed add, 2 MUFU.RCP, 1 packed fma
+// tanh of a packed pair of prescaled arguments (see tanh_prescaled), ONE reciprocal for both lanes:
+//   a_i = 1 + 2^(z_i);  r = 1 / (a_0 a_1);  1/a_0 = r a_1, 1/a_1 = r a_0;  tanh_i = 1 - 2 / a_i
+// 3 MUFU per pair instead of 4 (the XU pipe, 16 lanes/clk/SM, is the scarcest unit of this kernel).  The arguments are
+// clamped to 60 (tanh is already 1 - 2^-59 there, i.e. exactly 1.0f after rounding) so that a_0 a_1 <= 2^120 stays finite.
+#ifndef SRE_TANH_SHARED_RCP
+#define SRE_TANH_SHARED_RCP 1
+#endif
 SRE_DEV unsigned long long tanh2_prescaled(unsigned long long zs) {
-    float z0, z1, t0, t1, r0, r1;
+    float z0, z1, t0, t1;
     unpack2(zs, z0, z1);
+#if SRE_TANH_SHARED_RCP
+    z0 = fminf(z0, 60.0f);
+    z1 = fminf(z1, 60.0f);
+#endif
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(z0));
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(z1));
     float a0, a1;
     unpack2(add2(pack2(t0, t1), pack2(1.0f, 1.0f)), a0, a1);
+#if SRE_TANH_SHARED_RCP
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a0 * a1));
+    return fma2(pack2(r * a1, r * a0), pack2(-2.0f, -2.0f), pack2(1.0f, 1.0f));
+#else
+    float r0, r1;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(a0));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(a1));
     return fma2(pack2(r0, r1), pack2(-2.0f, -2.0f), pack2(1.0f, 1.0f));
+#endif
 }
 
 SRE_DEV void st_shared_v4(uint32_t addr, float a, float b, float c, float d) {
