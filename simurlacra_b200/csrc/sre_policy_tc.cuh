@@ -341,6 +341,7 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
     static constexpr int OFF_W3 = OFF_B2 + HID * 4;
     static constexpr int OFF_B3 = OFF_W3 + OUT * HID * 4;
     static constexpr int OFF_BAR = OFF_B3 + 16;             // two mbarriers (16 B) + TMEM base address (4 B)
+    static constexpr int OFF_CNT = OFF_BAR + 24;            // two arrival counters (one per K half)
     static constexpr int SMEM_BYTES = OFF_BAR + 32 + 1024;  // + slack for the manual 1024-byte alignment
     static constexpr float PRE = SRE_TANH_PRESCALE;
 
@@ -381,6 +382,8 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
         if (threadIdx.x == 0) {
             mbar_init(c.base + OFF_BAR, 1);
             mbar_init(c.base + OFF_BAR + 8, 1);
+            g[OFF_CNT / 4] = 0.f;  // bit pattern 0
+            g[OFF_CNT / 4 + 1] = 0.f;
         }
         if (threadIdx.x < 32) {
             asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c.base + OFF_BAR + 16),
@@ -438,12 +441,44 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
         if (!SINGLE_PASS) tmem_st8(t_lo, lo);
     }
 
-    SRE_DEV static bool forward(Ctx &c, const float *x, float *out, bool active) {
+    // Hand this warp's 32 rows of the A half to the tensor core.  No CTA barrier: every warp bumps an arrival counter
+    // and goes on; the warp that arrives LAST (fourth of the group) issues the 12 MMAs of the half and commits them to
+    // the half's mbarrier.  Groups cannot interleave: nobody gets past the mbarrier of a half before all four arrived.
+    SRE_DEV static void publish_half(Ctx &c, int half, uint32_t t_d, uint32_t t_ahi, uint32_t t_alo) {
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            uint32_t old;
+            asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;"
+                         : "=r"(old)
+                         : "r"(c.base + OFF_CNT + half * 4)
+                         : "memory");
+            if ((old & 3u) == 3u) {
+                tc_fence_after();
+                uint32_t acc = half;
+#pragma unroll
+                for (int pass = SINGLE_PASS ? 2 : 0; pass < 3; pass++) {
+                    const uint32_t a0 = pass == 0 ? t_alo : t_ahi;
+                    const uint32_t b0 = c.base + (pass == 1 ? OFF_B_LO : OFF_B_HI) + half * B_KB;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) {
+                        umma_tf32_ts(t_d, a0 + ks * 8, umma_desc_k_sw128(b0 + ks * 32), UMMA_IDESC_TF32_M128_N64, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit(c.base + OFF_BAR + half * 8);
+            }
+        }
+        __syncwarp();
+    }
+
+    // CTA-cooperative: all 128 threads call this every step (whole warps; warps need not be in lockstep).
+    SRE_DEV static void forward(Ctx &c, const float *x, float *out) {
         const int r = threadIdx.x;
         const float *sm = c.gen;
         const uint32_t lane_base = (uint32_t)(r & ~31) << 16;
         const uint32_t t_d = c.tmem, t_ahi = c.tmem + 64, t_alo = c.tmem + 96;
-        bool any = false;
         unsigned long long x2[IN];
 #pragma unroll
         for (int i = 0; i < IN; i++) x2[i] = pack2(x[i], x[i]);
@@ -460,25 +495,7 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
                 act_store8(a, lane_base + t_ahi + ch * 16, lane_base + t_alo + ch * 16);
                 act_store8(a + 4, lane_base + t_ahi + ch * 16 + 8, lane_base + t_alo + ch * 16 + 8);
             }
-            tmem_st_wait();
-            tc_fence_before();
-            if (half == 0) any = __syncthreads_or(active);
-            else __syncthreads();
-            if (threadIdx.x == 0) {
-                tc_fence_after();
-                uint32_t acc = half;
-#pragma unroll
-                for (int pass = SINGLE_PASS ? 2 : 0; pass < 3; pass++) {
-                    const uint32_t a0 = pass == 0 ? t_alo : t_ahi;
-                    const uint32_t b0 = c.base + (pass == 1 ? OFF_B_LO : OFF_B_HI) + half * B_KB;
-#pragma unroll
-                    for (int ks = 0; ks < 4; ks++) {
-                        umma_tf32_ts(t_d, a0 + ks * 8, umma_desc_k_sw128(b0 + ks * 32), UMMA_IDESC_TF32_M128_N64, acc);
-                        acc = 1;
-                    }
-                }
-                umma_commit(c.base + OFF_BAR + half * 8);
-            }
+            publish_half(c, half, t_d, t_ahi, t_alo);
         }
         mbar_wait(c.base + OFF_BAR + 8, c.parity);
         c.parity ^= 1;
@@ -516,8 +533,7 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
             unpack2(o2[q], e, od);
             out[q] = e + od;
         }
-        tc_fence_before();
-        return any;
+        tc_fence_before();  // orders this step's TMEM reads before the arrival that lets the next MMAs overwrite them
     }
 };
 

@@ -224,9 +224,12 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
 #pragma unroll
             for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
             if (TC) {
-                // CTA-cooperative (tcgen05): its barrier also tells whether any lane of the CTA is still running
-                const bool any = Tc::forward(tc, of, af, lane_state != IDLE);
-                if (!any && !record && !io.row_flag) break;  // CTA-uniform exit
+                // CTA-cooperative (tcgen05), no CTA barrier inside.  Every 16 rows the CTA agrees on whether any of
+                // its lanes is still running (the exit has to be CTA-uniform: all four warps feed each MMA)
+                if (!record && !io.row_flag && !io.auto_reset && (row & 15) == 0) {
+                    if (!__syncthreads_or(lane_state != IDLE)) break;
+                }
+                Tc::forward(tc, of, af);
             } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
             else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
             else linear_forward<DO, DA>(pol, sm_w, of, af);
