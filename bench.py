@@ -110,10 +110,14 @@ def cpu_port_run(workload, n_envs, horizon, threads, seed=0):
 
 
 def cpu_port_bounded(workload, horizon, threads, target_s=12.0):
-    steps, dt = cpu_port_run(workload, 256 * threads, horizon, threads)  # calibration
+    cpu_port_run(workload, 64 * threads, horizon, threads)  # thread-pool warm-up
+    steps, dt = cpu_port_run(workload, 2048 * threads, horizon, threads)  # calibration (about a second)
     rate = steps / dt
-    n = int(max(256 * threads, min(1 << 20, rate * target_s / horizon)))
+    n = int(max(256 * threads, min(1 << 21, rate * target_s / horizon)))
     steps, dt = cpu_port_run(workload, n, horizon, threads)
+    if dt < 0.7 * target_s:  # the calibration under-estimated the rate: one more, longer run (10-30 s of CPU work)
+        n = int(min(1 << 22, n * target_s / max(dt, 1e-3)))
+        steps, dt = cpu_port_run(workload, n, horizon, threads)
     return steps / dt, f"{n} envs x {horizon} steps (QQube + DR + FNN[64,64]) in {dt:.1f} s on {threads} threads", n
 
 
@@ -138,8 +142,9 @@ def run_reference_arm(args):
     line = dict(impl="reference", metric="env-steps/sec", value=value, unit="env-steps/s", n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=1e3 * tot_t / max(1, args.steps), higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="f64", data="synthetic",
-                config=dict(workload="QQubeSwingUpSim dt=1/250 H=600 + ActNorm + DomainRandWrapperLive(default qq) + FNN[64,64]",
-                            envs_per_step=n, horizon=horizon),
+                config=dict(workload="QQubeSwingUpSim dt=1/250 H=600 + ActNorm + DomainRandWrapperLive(default qq) + fused FNN[64,64]",
+                            envs_per_gpu=args.envs, horizon=horizon, auto_reset=True, trajectory="returns+lengths+stats",
+                            reference_sample_envs_per_step=n),
                 cpu_baseline=dict(value=value, unit="env-steps/s", cores=threads, kind="port", sample=sample),
                 e2e=dict(value=value, unit="env-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
@@ -167,6 +172,30 @@ def measure_fma_peak(E, L, torch, dev, dtype_code):
     return best / 1e12
 
 
+def measured_peaks():
+    """MEASURED_PEAKS.json (driver-written) or the fallback B200_PROFILING.md states."""
+    path = osp.join(ROOT, "MEASURED_PEAKS.json")
+    if osp.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d["bf16_tflops_sustained"]), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1400.0, source="fallback")
+
+
+def time_launches(torch, fn, k, flush):
+    """CUDA events around each of k launches on torch's current stream (the one the C-ABI launches on)."""
+    tot = 0.0
+    outs = []
+    for i in range(k):
+        flush.fill_(i & 0xFF)  # L2 flush between timed iterations (not timed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        outs.append(fn(i))
+        e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1) * 1e-3
+    return tot, outs
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -178,7 +207,10 @@ def main():
     ap.add_argument("--horizon", type=int, default=600)
     ap.add_argument("--hidden", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--precision", type=int, default=0, help="0 fp32 FMA, 1 tcgen05 3xTF32, 2 tcgen05 TF32")
+    ap.add_argument("--no-extras", action="store_true", help="skip the variant / trajectory-write measurements")
+    ap.add_argument("--precision", type=int, default=1,
+                    help="hidden layer of the fused policy: 0 fp32 FMA (CUDA cores), 1 tcgen05 3xTF32 (fp32-level "
+                         "accuracy, default), 2 tcgen05 single TF32")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
@@ -187,8 +219,16 @@ def main():
     import torch
     import torch.distributed as dist
 
+    import simurlacra_b200 as pyrado
     import simurlacra_b200.engine as E
     from simurlacra_b200 import _lib as L
+    from simurlacra_b200.domain_randomization.default_randomizers import (create_default_randomizer_qbb,
+                                                                           create_default_randomizer_qq)
+    from simurlacra_b200.environment_wrappers import ActNormWrapper, DomainRandWrapperLive
+    from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
+    from simurlacra_b200.environments.pysim.quanser_qube import QQubeSwingUpSim
+    from simurlacra_b200.policies import FNNPolicy
+    from simurlacra_b200.sampling import ParallelRolloutSampler
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -201,68 +241,71 @@ def main():
     N, H, hid = args.envs, args.horizon, args.hidden
     T = H + 1
     sizes = [6, hid, hid, 1]
-    w_host = torch.from_numpy(fnn_weights(sizes)).pin_memory()
-    w_dev = w_host.to(dev)
+    prec = args.precision if hid == 64 else 0
+    # ---- the workload through the reference-facing API (config C2 of BASELINE.json) ----
+    sim = QQubeSwingUpSim(dt=1 / 250.0, max_steps=H, device=dev, dtype=torch.float32)
+    env = DomainRandWrapperLive(ActNormWrapper(sim), create_default_randomizer_qq())
+    policy = FNNPolicy(env.spec, hidden_sizes=[hid, hid], hidden_nonlin=torch.tanh)  # parameters live on the host
+    policy.param_values = torch.from_numpy(fnn_weights(sizes))
+    policy.engine_precision = prec
+    sampler = ParallelRolloutSampler(env, policy, num_workers=1, min_rollouts=1, seed=0)
+    # device-resident descriptors for the `value` measurement
+    w_dev = torch.from_numpy(fnn_weights(sizes)).to(dev)
     cfg = E.make_cfg(L.QQ, 1 / 250.0, H, dtype=torch.float32, act_norm=True)
     distr = E.make_distr_table(qq_randomizer(E.nominal_params(L.QQ)))
-    pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes, precision=args.precision)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    launches = [0]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def one_step(i, e2e):
-        """One pass of the hot path. Device-resident variant (e2e=False) or through host buffers (e2e=True)."""
-        if e2e:
-            w_dev.copy_(w_host, non_blocking=True)  # policy update: pinned host -> device (the reference pickles
-            # the state_dict to every worker each sample(), parallel_rollout_sampler.py:269)
+    def resident_step(i, precision):
+        pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes, precision=precision)
         res = E.rollout(cfg, pol, N, T, device=dev, distr=distr, seed=i, env_offset=rank * N, auto_reset=True,
                         record=False)
+        launches[0] += L.lib().sre_last_launch_count()
         if world > 1:  # the statistics the learner logs: one small NCCL all-reduce (SURVEY 8e)
             dist.all_reduce(res["stats"][:6])
-        if e2e:
-            return res["ret"].cpu(), res["length"].cpu(), res["stats"].cpu()
-        return res
+        return res["stats"]
 
-    # ---- device-resident timing ----
+    def e2e_step(i):
+        """The call a user makes: policy parameters on the host (pinned staging -> H2D inside), results to the host."""
+        res = sampler.sample_batch(N, auto_reset=True)
+        return res["ret"].cpu(), res["length"].cpu(), sampler.last_stats.cpu()
+
+    def timed(fn, k):
+        barrier()
+        t, outs = time_launches(torch, fn, k, flush)
+        barrier()
+        if world > 1:
+            tt = torch.tensor([t], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t = float(tt)
+        return t, outs
+
+    # ---- device-resident timing (value) ----
     for i in range(args.warmup):
-        one_step(i, False)
+        resident_step(i, prec)
     clocks = ClockSampler(local)
-    barrier()
+    launches[0] = 0
     if rank == 0:
         clocks.start()
-    ev = []
-    total_env_steps = 0.0
-    for i in range(args.steps):
-        flush.fill_(i & 0xFF)  # L2 flush between timed iterations (not timed)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        res = one_step(args.warmup + i, False)
-        e1.record()
-        ev.append((e0, e1, res["stats"]))
-    barrier()
+    t_dev, stats = timed(lambda i: resident_step(args.warmup + i, prec), args.steps)
     clk = clocks.stop() if rank == 0 else None
-    t_dev = sum(a.elapsed_time(b) for a, b, _ in ev) * 1e-3
-    steps_dev = sum(float(s[L.STAT_STEPS]) for _, _, s in ev)  # after the all-reduce: whole job
-    if world == 1:
-        total_env_steps = steps_dev
-    else:
-        total_env_steps = steps_dev  # stats were all-reduced: already the sum over ranks
-        tt = torch.tensor([t_dev], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_dev = float(tt)
+    n_launches = launches[0]
+    total_env_steps = sum(float(s[L.STAT_STEPS]) for s in stats) * (1 if world > 1 else 1)  # all-reduced: whole job
     value = total_env_steps / t_dev
 
-    # ---- end-to-end through host buffers ----
+    # ---- end-to-end through the public sampler call with host buffers ----
     for i in range(2):
-        one_step(i, True)
+        e2e_step(i)
     barrier()
     t0 = time.perf_counter()
     e2e_steps = 0.0
     for i in range(args.steps):
-        ret_h, len_h, st_h = one_step(100 + i, True)
+        ret_h, len_h, st_h = e2e_step(i)
         e2e_steps += float(st_h[L.STAT_STEPS])
     barrier()
     t_e2e = time.perf_counter() - t0
@@ -272,25 +315,80 @@ def main():
         t_e2e = float(tt)
     e2e_value = e2e_steps / t_e2e
 
+    extras = {}
     if rank == 0:
-        # kernel time == step time here: the step is a single kernel launch
+        peaks = measured_peaks()
         fma_peak = measure_fma_peak(E, L, torch, dev, L.F32)
-        per_rank_steps = total_env_steps / world
+        per_rank_rate = value / world
         flop = FLOP_PER_STEP["qq"] if hid == 64 else 120 + 2 * (6 * hid + hid * hid + hid) + 2 * hid + 1
-        achieved = per_rank_steps * flop / t_dev / 1e12
+        achieved = per_rank_rate * flop / 1e12
+        prec_name = {0: "fp32 FMA (CUDA cores)", 1: "tcgen05 3xTF32 split (fp32-level accuracy)", 2: "tcgen05 TF32"}[prec]
+        roofline = dict(bound="fp32_fma", achieved=achieved, peak=fma_peak, unit="TFLOP/s", frac=achieved / fma_peak,
+                        traffic=None, flop_per_env_step=flop,
+                        peak_source="measured live: FMA-only kernel (sre_bench_fma), best of 4; MEASURED_PEAKS.json has "
+                                    "no FP32 figure",
+                        note="algorithmic FLOP (SURVEY 8d) of env + FNN per env-step over the FP32 CUDA-core FMA peak; "
+                             "with the hidden layer on the tensor cores this fraction can exceed 1 (see roofline_tensor)")
+        if prec > 0:
+            passes = 3 if prec == 1 else 1
+            t_ach = per_rank_rate * passes * 2 * hid * hid / 1e12
+            t_peak = peaks["bf16_tflops"] / 2  # TF32 dense = half the bf16 rate
+            extras["roofline_tensor"] = dict(bound="tensor", achieved=t_ach, peak=t_peak, unit="TFLOP/s",
+                                             frac=t_ach / t_peak, traffic=None,
+                                             note=f"tcgen05.mma kind::tf32 FLOP actually issued ({passes} pass(es) of the "
+                                                  f"64x64 layer) over half the {peaks['source']} sustained bf16 peak; the "
+                                                  f"kernel is bound by issue slots and the MUFU pipe (tanh), not by the "
+                                                  f"tensor pipe")
         line = dict(metric="env-steps/sec", value=value, unit="env-steps/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=1e3 * t_dev / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f32", data="synthetic",
                     config=dict(workload=f"QQubeSwingUpSim dt=1/250 H={H} + ActNorm + DomainRandWrapperLive(default qq) + fused FNN[{hid},{hid}]",
                                 envs_per_gpu=N, horizon=H, auto_reset=True, trajectory="returns+lengths+stats",
+                                policy_hidden_layer=prec_name,
                                 l2="flushed between timed iterations (256 MB fill)", parallelism=f"env-shard x{world}"),
-                    e2e=dict(value=e2e_value, unit="env-steps/s", h2d_bytes_per_step=int(w_host.numel() * 4),
+                    e2e=dict(value=e2e_value, unit="env-steps/s", h2d_bytes_per_step=int(policy.num_param * 4),
                              d2h_bytes_per_step=int(N * 8 + 64)),
-                    gpu_launches=args.steps,
-                    clocks=clk,
-                    roofline=dict(bound="fp32_fma", achieved=achieved, peak=fma_peak, unit="TFLOP/s", frac=achieved / fma_peak,
-                                  traffic=None, flop_per_env_step=flop,
-                                  peak_source="measured live: FMA-only kernel (sre_bench_fma), best of 4; MEASURED_PEAKS.json has no FP32 figure"))
+                    gpu_launches=n_launches, clocks=clk, roofline=roofline)
+
+    # ---- extras on one GPU: the other arithmetic variant, and the trajectory-write (HBM) workload ----
+    if world == 1 and not args.no_extras:
+        other = 0 if prec else 1
+        if hid == 64:
+            for i in range(3):
+                resident_step(i, other)
+            t_o, st_o = timed(lambda i: resident_step(50 + i, other), args.steps)
+            rate_o = sum(float(s[L.STAT_STEPS]) for s in st_o) / t_o
+            extras["variants"] = {("fp32_fma" if other == 0 else "tcgen05_tf32x3"): dict(
+                value=rate_o, unit="env-steps/s", fma_roofline_frac=rate_o * flop / 1e12 / fma_peak)}
+        # config C4: QBallBalancerSim + DR (20 params) + cheap fused policy, FULL StepSequence records written to HBM
+        qn, qh = min(N, 1 << 20), 500
+        qcfg = E.make_cfg(L.QBB, 0.01, qh, dtype=torch.float32, act_norm=True)
+        qdistr = create_default_randomizer_qbb().table(QBallBalancerSim._param_names)
+        qsizes = [8, 16, 16, 2]
+        qpol = E.make_policy(L.POL_FNN, torch.from_numpy(fnn_weights(qsizes, seed=1)).to(dev), sizes=qsizes)
+        lay = E.record_layout(L.QBB)
+        traj = torch.empty(qh + 1, qn, lay["width"], dtype=torch.float32, device=dev)
+        flag = torch.empty(qh + 1, qn, dtype=torch.uint8, device=dev)
+
+        def qstep(i):
+            return E.rollout(qcfg, qpol, qn, qh + 1, device=dev, distr=qdistr, seed=i, auto_reset=True, record=True,
+                             traj=traj, row_flag=flag)["stats"]
+
+        for i in range(2):
+            qstep(i)
+        t_q, st_q = timed(lambda i: qstep(10 + i), 3)
+        bytes_per_launch = (qh + 1) * qn * (lay["width"] * 4 + 1)
+        gbs = 3 * bytes_per_launch / t_q / 1e9
+        extras["roofline_traj"] = dict(bound="hbm", achieved=gbs, peak=peaks["hbm_gbs"], unit="GB/s", frac=gbs / peaks["hbm_gbs"],
+                                       traffic=None, peak_source=f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']})",
+                                       workload=f"QBallBalancerSim dt=0.01 H={qh} + ActNorm + DR(default qbb, 20 params) + fused "
+                                                f"FNN[16,16], {qn} envs, records [T,N,{lay['width']}] f32 + flags written",
+                                       bytes_per_env_step=lay["width"] * 4 + 1,
+                                       env_steps_per_s=sum(float(s[L.STAT_STEPS]) for s in st_q) / t_q)
+        del traj, flag
+
+    if rank == 0:
+        line.update(extras)
         if not args.no_cpu_baseline and world == 1:
             threads = os.cpu_count() or 1
             v, sample, _ = cpu_port_bounded("qq", H, threads)

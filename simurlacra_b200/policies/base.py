@@ -40,6 +40,11 @@ class Policy(nn.Module, ABC):
         if use_cuda and not torch.cuda.is_available():
             warn("Tried to run on CUDA, but it is not available. Falling back to CPU.")
         self._device = "cuda" if use_cuda and torch.cuda.is_available() else "cpu"
+        # arithmetic of the fused hidden layer (engine extension): L.PREC_FP32 (CUDA-core FMA, default),
+        # L.PREC_TF32X3 (tcgen05 tensor cores, 3 x TF32 split, fp32-level accuracy) or L.PREC_TF32
+        self.engine_precision = L.PREC_FP32
+        self._pinned = None
+        self._dev_weights = {}
 
     @property
     def device(self) -> str:
@@ -104,8 +109,22 @@ class Policy(nn.Module, ABC):
         return None
 
     def _engine_weights(self, device) -> torch.Tensor:
+        """The flat float32 parameter vector on `device`.  Host-resident parameters travel through a pinned staging
+        buffer into a persistent device buffer (one asynchronous H2D copy per call = the per-`sample()` policy
+        update that the reference does by pickling the state_dict to every worker)."""
         with torch.no_grad():
-            return self.param_values.detach().to(device=device, dtype=torch.float32).contiguous()
+            v = self.param_values.detach()
+            if v.is_cuda:
+                return v.to(device=device, dtype=torch.float32).contiguous()
+            device = torch.device(device)
+            if self._pinned is None or self._pinned.numel() != v.numel():
+                self._pinned = torch.empty(v.numel(), dtype=torch.float32).pin_memory()
+            self._pinned.copy_(v)
+            dev = self._dev_weights.get(device)
+            if dev is None or dev.numel() != v.numel():
+                dev = self._dev_weights[device] = torch.empty(v.numel(), dtype=torch.float32, device=device)
+            dev.copy_(self._pinned, non_blocking=True)
+            return dev
 
     def forward_engine(self, obs: torch.Tensor) -> torch.Tensor:
         """Batch forward pass with the CUDA kernel: obs float32 CUDA [N, obs_dim] -> act float32 [N, act_dim]."""

@@ -134,4 +134,5 @@ class FNNPolicy(Policy):
         if codes is None:
             return None
         return E.make_policy(L.POL_FNN, self._engine_weights(device), sizes=self.net.sizes, hidden_nonlin=codes[0],
-                             output_nonlin=codes[1], cartpole_feats=self.cartpole_feats)
+                             output_nonlin=codes[1], cartpole_feats=self.cartpole_feats,
+                             precision=self.engine_precision)
