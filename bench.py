@@ -11,8 +11,12 @@ auto-reset so that every lane steps for the whole horizon).  Prints ONE JSON lin
  value      env-steps/s, whole job, inputs resident in HBM (device-timed with CUDA events, max over ranks)
  e2e        the same through the public sampler call with HOST buffers: policy parameters copied from pinned host
             memory every step, returns / lengths / statistics read back to the host every step
- roofline   FP32-FMA roofline of the rollout kernel; the peak is MEASURED live with an FMA-only kernel because
-            MEASURED_PEAKS.json carries no FP32 figure
+ roofline   of the rollout kernel: algorithmic FLOP per env-step (9 337) x env-steps/s over the TF32
+            tensor peak (half of MEASURED_PEAKS.json's bf16 figure) when the hidden layer runs on tcgen05;
+ roofline_fp32  the same FLOP over the FP32-FMA peak MEASURED live with an FMA-only kernel (MEASURED_PEAKS.json
+            carries no FP32 figure) -- the CUDA-core view, and the primary roofline with --precision 0
+ roofline_traj  HBM roofline of the trajectory-write workload (QBB records)
+ variants   the other arithmetic (--precision 0: packed fp32 FMA on the CUDA cores)
  cpu_baseline  the CPU oracle port (oracle/sre_oracle.c, OpenMP) on a bounded sample of the same workload
 
 --impl reference times the reference's CPU implementation of the path.  The reference is Python and does not
@@ -323,22 +327,31 @@ def main():
         flop = FLOP_PER_STEP["qq"] if hid == 64 else 120 + 2 * (6 * hid + hid * hid + hid) + 2 * hid + 1
         achieved = per_rank_rate * flop / 1e12
         prec_name = {0: "fp32 FMA (CUDA cores)", 1: "tcgen05 3xTF32 split (fp32-level accuracy)", 2: "tcgen05 TF32"}[prec]
-        roofline = dict(bound="fp32_fma", achieved=achieved, peak=fma_peak, unit="TFLOP/s", frac=achieved / fma_peak,
-                        traffic=None, flop_per_env_step=flop,
-                        peak_source="measured live: FMA-only kernel (sre_bench_fma), best of 4; MEASURED_PEAKS.json has "
-                                    "no FP32 figure",
-                        note="algorithmic FLOP (SURVEY 8d) of env + FNN per env-step over the FP32 CUDA-core FMA peak; "
-                             "with the hidden layer on the tensor cores this fraction can exceed 1 (see roofline_tensor)")
+        fp32_roof = dict(bound="fp32_fma", achieved=achieved, peak=fma_peak, unit="TFLOP/s", frac=achieved / fma_peak,
+                         traffic=None, flop_per_env_step=flop,
+                         peak_source="measured live: FMA-only kernel (sre_bench_fma), best of 4; MEASURED_PEAKS.json has "
+                                     "no FP32 figure",
+                         note="algorithmic FLOP (SURVEY 8d) of env + FNN per env-step over the FP32 CUDA-core FMA peak; "
+                              "with the hidden layer on the tensor cores this fraction can exceed 1")
         if prec > 0:
+            # the dominant kernel runs its 64x64 layer on tcgen05: report it against the tensor roofline (TF32 dense =
+            # half the measured bf16 rate); `achieved` is ALGORITHMIC flop (one fp32 product per weight), `issued`
+            # counts the 3 TF32 passes of the split actually executed.
             passes = 3 if prec == 1 else 1
-            t_ach = per_rank_rate * passes * 2 * hid * hid / 1e12
-            t_peak = peaks["bf16_tflops"] / 2  # TF32 dense = half the bf16 rate
-            extras["roofline_tensor"] = dict(bound="tensor", achieved=t_ach, peak=t_peak, unit="TFLOP/s",
-                                             frac=t_ach / t_peak, traffic=None,
-                                             note=f"tcgen05.mma kind::tf32 FLOP actually issued ({passes} pass(es) of the "
-                                                  f"64x64 layer) over half the {peaks['source']} sustained bf16 peak; the "
-                                                  f"kernel is bound by issue slots and the MUFU pipe (tanh), not by the "
-                                                  f"tensor pipe")
+            t_peak = peaks["bf16_tflops"] / 2
+            t_iss = per_rank_rate * passes * 2 * hid * hid / 1e12
+            roofline = dict(bound="tensor", achieved=achieved, peak=t_peak, unit="TFLOP/s", frac=achieved / t_peak,
+                            traffic=None, flop_per_env_step=flop, issued=t_iss, frac_issued=t_iss / t_peak,
+                            peak_source=f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}) / 2: kind::tf32 "
+                                        f"runs at half the bf16 rate",
+                            note=f"{passes} tcgen05.mma kind::tf32 pass(es) per 64x64 layer (3xTF32 split keeps fp32-level "
+                                 f"accuracy); per env-step only 8192 of {flop} FLOP are GEMM-shaped, the rest (layer 1, "
+                                 f"128 tanh, layer 3, dynamics, sincos, reward) runs on the CUDA cores: ncu shows issue "
+                                 f"slots 52% and the MUFU pipe 42% busy, tensor pipe 19% (profiles/r01_f_*), so the "
+                                 f"kernel is CUDA-core/MUFU bound -- see roofline_fp32")
+            extras["roofline_fp32"] = fp32_roof
+        else:
+            roofline = fp32_roof
         line = dict(metric="env-steps/sec", value=value, unit="env-steps/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                     ms_per_step=1e3 * t_dev / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f32", data="synthetic",
