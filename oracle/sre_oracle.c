@@ -712,10 +712,12 @@ static inline double u53(uint32_t a, uint32_t b) {
 }
 static inline float u24(uint32_t a) { return (float)(a >> 8) * (1.0f / 16777216.0f); }
 static inline double normal_d(uint32_t a, uint32_t b) {
-    /* Box-Muller in fp64: u1 in (0,1], u2 in [0,1) */
-    double u1 = ((double)a + 1.0) * (1.0 / 4294967296.0);
-    double u2 = (double)b * (1.0 / 4294967296.0);
-    return sqrt(-2.0 * log(u1)) * cos(2.0 * M_PI * u2);
+    /* Box-Muller, engine RNG specification: u1 = (2 (a >> 9) + 1) / 2^24 in (0,1), x = ((int32) b >> 8) / 2^23 in
+     * [-1,1), z = sqrt(-2 ln u1) cos(pi x).  Evaluated in fp64 here; the engine evaluates the same expression in
+     * float32 on the (exactly representable) inputs. */
+    double u1 = (double)(2u * (a >> 9) + 1u) * (1.0 / 16777216.0);
+    double x = (double)((int32_t)b >> 8) * (1.0 / 8388608.0);
+    return sqrt(-2.0 * log(u1)) * cos(M_PI * x);
 }
 
 /* Distribution table entry (engine spec, mirrors DomainParam fields: domain_parameter.py:46-76,

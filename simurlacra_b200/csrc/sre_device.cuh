@@ -75,11 +75,15 @@ SRE_DEV double u53(uint32_t a, uint32_t b) {
     return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) * (1.0 / 9007199254740992.0);
 }
 SRE_DEV float u24(uint32_t a) { return (float)(a >> 8) * (1.0f / 16777216.0f); }
-// Box-Muller in fp64 (once per episode and parameter: accuracy matters more than speed)
-SRE_DEV double normal_d(uint32_t a, uint32_t b) {
-    double u1 = ((double)a + 1.0) * (1.0 / 4294967296.0);
-    double u2 = (double)b * (1.0 / 4294967296.0);
-    return sqrt(-2.0 * log(u1)) * cos(2.0 * SRE_PI * u2);
+// Standard normal for a domain parameter (engine RNG specification, restated in fp64 by the CPU checker):
+//   u1 = (2 (a >> 9) + 1) / 2^24 in (0, 1),  x = ((int32) b >> 8) / 2^23 in [-1, 1),  z = sqrt(-2 ln u1) cos(pi x).
+// Both inputs are EXACT float32 numbers (odd 24-bit integer, signed 24-bit integer), so float32 logf / sqrtf / cospif
+// reproduce the fp64 evaluation to a few float32 ulp -- an episode start costs no fp64 instructions (the fp64 pipe
+// of sm_100 made resets the most expensive rows of the kernel).  |z| <= sqrt(48 ln 2) = 5.77.
+SRE_DEV float normal_f(uint32_t a, uint32_t b) {
+    const float u1 = (float)(2u * (a >> 9) + 1u) * (1.0f / 16777216.0f);
+    const float x = (float)((int32_t)b >> 8) * (1.0f / 8388608.0f);
+    return __fmul_rn(sqrtf(-2.0f * logf(u1)), cospif(x));
 }
 
 // DomainParam.sample for one table entry (domain_parameter.py:104-132): float32 draw like torch's default
@@ -88,7 +92,7 @@ SRE_DEV float sample_entry(const sre_distr &d, uint64_t seed, uint64_t env, uint
     u32x4 x = rng_block(seed, env, episode, SRE_STREAM_PARAMS, entry);
     float s;
     if (d.kind == SRE_DISTR_NORMAL) {
-        float z = (float)normal_d(x.x, x.y);
+        float z = normal_f(x.x, x.y);
         s = __fadd_rn(d.a, __fmul_rn(d.b, z));
     } else if (d.kind == SRE_DISTR_UNIFORM) {
         float u = u24(x.x);

@@ -265,7 +265,7 @@ with torch.no_grad():
 sharding.broadcast_policy(lin, src=0)
 assert float(lin.weight[0, 0]) == 1.0
 dist.barrier(); dist.destroy_process_group()
-print("rank", rank, "ok")
+sys.stdout.write(f"rank {rank} ok\n"); sys.stdout.flush()
 """
 
 
