@@ -42,6 +42,10 @@ QQ_NAMES = ["gravity_const", "motor_resistance", "motor_back_emf", "mass_rot_pol
 # algorithmic work per env-step (FLOP convention stated there): env + fused FNN [64,64]
 FLOP_PER_STEP = {"qq": 120 + 9217, "qcp": 375 + 9089, "qbb": 260 + 2 * (8 * 16 + 16 * 16 + 16 * 2) + 34}
 RECORD_BYTES = {"qq": 53, "qcp": 53, "qbb": 93}
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of rollout_kernel<QQ, float, tcgen05> at the default size
+# (2^20 envs x 600 steps), from the ncu --set full capture summarised in profiles/r01_g_tc_f32reset_rollout_qq_fnn64_1M.txt
+# (132 352 B read + 5 444 608 B written: returns, lengths, first-episode parameters; the state never leaves the registers)
+NCU_TRAFFIC = {(1 << 20, 600, 64, 1): 132352 + 5444608}
 
 
 def qq_randomizer(nom):
@@ -341,7 +345,8 @@ def main():
             t_peak = peaks["bf16_tflops"] / 2
             t_iss = per_rank_rate * passes * 2 * hid * hid / 1e12
             roofline = dict(bound="tensor", achieved=achieved, peak=t_peak, unit="TFLOP/s", frac=achieved / t_peak,
-                            traffic=None, flop_per_env_step=flop, issued=t_iss, frac_issued=t_iss / t_peak,
+                            traffic=NCU_TRAFFIC.get((N, H, hid, prec)),
+                            traffic_source="profiles/r01_g_tc_f32reset_rollout_qq_fnn64_1M.txt (bytes per launch)", flop_per_env_step=flop, issued=t_iss, frac_issued=t_iss / t_peak,
                             peak_source=f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}) / 2: kind::tf32 "
                                         f"runs at half the bf16 rate",
                             note=f"{passes} tcgen05.mma kind::tf32 pass(es) per 64x64 layer (3xTF32 split keeps fp32-level "
