@@ -378,6 +378,19 @@ def main():
             rate_o = sum(float(s[L.STAT_STEPS]) for s in st_o) / t_o
             extras["variants"] = {("fp32_fma" if other == 0 else "tcgen05_tf32x3"): dict(
                 value=rate_o, unit="env-steps/s", fma_roofline_frac=rate_o * flop / 1e12 / fma_peak)}
+
+            # the same launch with step-based exploration in the loop (NormalActNoiseExplStrat, std 0.1): one Philox
+            # block + one Box-Muller pair per env-step on top of the policy
+            def explore_step(i):
+                pol = E.make_policy(L.POL_FNN, w_dev, sizes=sizes, precision=prec, act_noise=L.ACT_NOISE_NORMAL,
+                                    act_noise_scale=[0.1])
+                return E.rollout(cfg, pol, N, T, device=dev, distr=distr, seed=i, auto_reset=True, record=False)["stats"]
+
+            for i in range(3):
+                explore_step(i)
+            t_x, st_x = timed(lambda i: explore_step(70 + i), args.steps)
+            extras["variants"]["normal_act_noise"] = dict(value=sum(float(s[L.STAT_STEPS]) for s in st_x) / t_x,
+                                                          unit="env-steps/s", note="headline arithmetic + exploration noise")
         # config C4: QBallBalancerSim + DR (20 params) + cheap fused policy, FULL StepSequence records written to HBM
         qn, qh = min(N, 1 << 20), 500
         qcfg = E.make_cfg(L.QBB, 0.01, qh, dtype=torch.float32, act_norm=True)

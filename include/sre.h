@@ -72,6 +72,9 @@ extern "C" {
 #define SRE_POL_IDLE 3    /* policies/feed_forward/dummy.py (IdlePolicy): zero action */
 
 /* sre_policy.precision */
+#define SRE_ACT_NOISE_NONE 0
+#define SRE_ACT_NOISE_NORMAL 1
+#define SRE_ACT_NOISE_UNIFORM 2
 #define SRE_PREC_FP32 0   /* FP32 FMA on the CUDA cores (bias first, inputs ascending) */
 #define SRE_PREC_TF32X3 1 /* tcgen05 tensor cores, 3 x TF32 split (hi*hi + hi*lo + lo*hi): fp32-level accuracy */
 #define SRE_PREC_TF32 2   /* tcgen05 tensor cores, single TF32 pass (about 1e-3 relative) */
@@ -182,6 +185,15 @@ typedef struct sre_policy {
     int32_t precision;                /* SRE_PREC_*: arithmetic of the 64x64 hidden layer (float builds, [in,64,64,out] tanh) */
     const float *weights;             /* device; torch layout W[out][in], bias[out], layers concatenated */
     int64_t n_weights;
+    /* Step-based exploration fused into sre_rollout (StochasticActionExplStrat.forward,
+     * exploration/stochastic_action.py:68-94): act = dist(policy(obs) + mean).rsample(), float32 like torch.
+     * SRE_ACT_NOISE_NORMAL: NormalActNoiseExplStrat / DiagNormalNoise (stochastic_action.py:121, normal_noise.py:155),
+     * act_noise_scale = std.  SRE_ACT_NOISE_UNIFORM: UniformActNoiseExplStrat (stochastic_action.py:183,
+     * uniform_noise.py:160), act_noise_scale = halfspan.  Philox stream SRE act-noise, block = step index. */
+    int32_t act_noise;
+    int32_t reserved;
+    float act_noise_scale[SRE_MAX_DA];
+    float act_noise_mean[SRE_MAX_DA];
 } sre_policy;
 
 /* Inputs / outputs of one rollout launch.  Replaces rollout() (sampling/rollout.py:63) run for N envs by

@@ -57,6 +57,9 @@ class Policy(C.Structure):
         ("output_nonlin", C.c_int),
         ("cartpole_feats", C.c_int),
         ("weights", C.POINTER(C.c_float)),
+        ("act_noise", C.c_int),
+        ("act_noise_scale", C.c_float * 2),
+        ("act_noise_mean", C.c_float * 2),
     ]
 
 
@@ -183,8 +186,14 @@ def make_distr_table(entries):
     return arr
 
 
-def make_policy(kind, weights=None, sizes=(), feats=(), hidden_nonlin=0, output_nonlin=0, cartpole_feats=False):
+def make_policy(kind, weights=None, sizes=(), feats=(), hidden_nonlin=0, output_nonlin=0, cartpole_feats=False,
+                act_noise=0, act_noise_scale=(), act_noise_mean=()):
     p = Policy()
+    p.act_noise = int(act_noise)
+    for i, v in enumerate(act_noise_scale):
+        p.act_noise_scale[i] = v
+    for i, v in enumerate(act_noise_mean):
+        p.act_noise_mean[i] = v
     p.kind = kind
     p.n_layers = max(len(sizes) - 1, 0)
     for i, s in enumerate(sizes):

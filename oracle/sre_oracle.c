@@ -845,6 +845,12 @@ typedef struct {
     int output_nonlin;     /* 0 none, 1 tanh */
     int cartpole_feats;    /* fork's FNNPolicy input transform, fnn.py:214-218 */
     const float *weights;
+    /* StochasticActionExplStrat.forward (exploration/stochastic_action.py:68-94): 0 none, 1 NormalActNoiseExplStrat
+     * (act_noise_scale = std, normal_noise.py:155-163), 2 UniformActNoiseExplStrat (scale = halfspan,
+     * uniform_noise.py:160-168); act_noise_mean = the learnable noise mean (train_mean) */
+    int act_noise;
+    float act_noise_scale[2];
+    float act_noise_mean[2];
 } orc_policy;
 
 static float nonlin_f(int kind, float x) {
@@ -1004,6 +1010,33 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
                 float of[ORC_MAX_DO], af[ORC_MAX_DA];
                 for (int i = 0; i < dob; i++) of[i] = (float)obs[i];
                 orc_policy_forward(pol, of, dob, af, da);
+                if (pol->act_noise) {
+                    /* act = dist(policy(obs) + mean).rsample(), float32 with torch's roundings; one Philox block per
+                     * step (engine RNG specification): normal pair from words 0,1 with the exactly representable
+                     * inputs of normal_d (evaluated in fp64 here, float32 on the engine); uniforms from words 0,1 */
+                    uint32_t x[4];
+                    orc_rng(cfg->seed, genv, cfg->episode, ORC_STREAM_ACT_NOISE, (uint32_t)t, x);
+                    if (pol->act_noise == 1) {
+                        double u1 = (double)(2u * (x[0] >> 9) + 1u) * (1.0 / 16777216.0);
+                        double ang = (double)((int32_t)x[1] >> 8) * (1.0 / 8388608.0);
+                        double r = sqrt(-2.0 * log(u1));
+                        float z[2] = {(float)(r * cos(M_PI * ang)), (float)(r * sin(M_PI * ang))};
+                        for (int i = 0; i < da; i++) {
+                            float loc = af[i] + pol->act_noise_mean[i];
+                            float sc = z[i] * pol->act_noise_scale[i];
+                            af[i] = loc + sc;
+                        }
+                    } else {
+                        float u[2] = {u24(x[0]), u24(x[1])};
+                        for (int i = 0; i < da; i++) {
+                            float loc = af[i] + pol->act_noise_mean[i];
+                            float lo = loc - pol->act_noise_scale[i], hi = loc + pol->act_noise_scale[i];
+                            float w = hi - lo;
+                            float sc = u[i] * w;
+                            af[i] = lo + sc;
+                        }
+                    }
+                }
                 for (int i = 0; i < da; i++) act[i] = (double)af[i];
             }
             double act_env[ORC_MAX_DA];

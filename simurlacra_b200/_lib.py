@@ -21,6 +21,7 @@ REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2
 FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8, 16
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3
 PREC_FP32, PREC_TF32X3, PREC_TF32 = 0, 1, 2
+ACT_NOISE_NONE, ACT_NOISE_NORMAL, ACT_NOISE_UNIFORM = 0, 1, 2
 FEATS = dict(const=0, identity=1, sign=2, abs=3, squared=4, cubic=5, sin=6, cos=7, sinsin=8, sincos=9)
 DISTR_NORMAL, DISTR_UNIFORM, DISTR_BERNOULLI = 0, 1, 2
 ROW_STEP, ROW_DONE, ROW_TERMINAL, ROW_TRUNCATED, ROW_IDLE = 0, 1, 2, 3, 4
@@ -91,6 +92,10 @@ class Policy(C.Structure):
         ("precision", C.c_int32),
         ("weights", C.c_void_p),
         ("n_weights", C.c_int64),
+        ("act_noise", C.c_int32),
+        ("reserved", C.c_int32),
+        ("act_noise_scale", C.c_float * MAX_DA),
+        ("act_noise_mean", C.c_float * MAX_DA),
     ]
 
 

@@ -45,6 +45,18 @@ int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp) {
     memset(&kp, 0, sizeof kp);
     SRE_CHECK_ARG(pol != nullptr, SRE_E_POLICY, "policy is NULL");
     kp.kind = pol->kind;
+    SRE_CHECK_ARG(pol->act_noise >= SRE_ACT_NOISE_NONE && pol->act_noise <= SRE_ACT_NOISE_UNIFORM, SRE_E_POLICY,
+                  "unknown act_noise %d", pol->act_noise);
+    SRE_CHECK_ARG(pol->act_noise == SRE_ACT_NOISE_NONE || pol->kind == SRE_POL_FNN || pol->kind == SRE_POL_LINEAR,
+                  SRE_E_UNSUPPORTED, "exploration noise needs an FNN or Linear policy");
+    kp.act_noise = pol->act_noise;
+    for (int i = 0; i < SRE_MAX_DA; i++) {
+        if (pol->act_noise != SRE_ACT_NOISE_NONE && i < n_act)
+            SRE_CHECK_ARG(pol->act_noise_scale[i] > 0.f, SRE_E_POLICY, "act_noise_scale[%d] = %g must be > 0", i,
+                          (double)pol->act_noise_scale[i]);
+        kp.noise_scale[i] = pol->act_noise_scale[i];
+        kp.noise_mean[i] = pol->act_noise_mean[i];
+    }
     if (pol->kind == SRE_POL_ACTIONS || pol->kind == SRE_POL_IDLE) return 0;
     SRE_CHECK_ARG(pol->weights != nullptr, SRE_E_POLICY, "policy weights are NULL");
     long long need = 0;

@@ -237,4 +237,29 @@ SRE_DEV void add_obs_noise(const KCfg<R> &cfg, uint64_t seed, uint64_t env, uint
     }
 }
 
+// StochasticActionExplStrat.forward (exploration/stochastic_action.py:68-94): act = dist(policy(obs) + mean).rsample() in
+// float32 with torch's roundings -- Normal.rsample: loc + eps * scale; Uniform.rsample: low + rand * (high - low) with
+// low/high = loc -/+ halfspan.  One Philox block per (env, episode, step): words (x, y) -> the normal pair, or x, y ->
+// the two uniforms.
+template <int DA>
+SRE_DEV void add_act_noise(int kind, const float *scale, const float *mean, uint64_t seed, uint64_t env, uint32_t episode,
+                           uint32_t t, float *act) {
+    static_assert(DA <= 2, "one Philox block carries the noise of at most two action dimensions");
+    const u32x4 x = rng_block(seed, env, episode, SRE_STREAM_ACT_NOISE, t);
+    if (kind == SRE_ACT_NOISE_NORMAL) {
+        float z[2];
+        normal2_f(x.x, x.y, z[0], z[1]);
+#pragma unroll
+        for (int i = 0; i < DA; i++) act[i] = __fadd_rn(__fadd_rn(act[i], mean[i]), __fmul_rn(z[i], scale[i]));
+    } else {
+        const float u[2] = {u24(x.x), u24(x.y)};
+#pragma unroll
+        for (int i = 0; i < DA; i++) {
+            const float loc = __fadd_rn(act[i], mean[i]);
+            const float lo = __fsub_rn(loc, scale[i]), hi = __fadd_rn(loc, scale[i]);
+            act[i] = __fadd_rn(lo, __fmul_rn(u[i], __fsub_rn(hi, lo)));
+        }
+    }
+}
+
 }  // namespace sre

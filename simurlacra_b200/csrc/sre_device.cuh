@@ -86,6 +86,17 @@ SRE_DEV float normal_f(uint32_t a, uint32_t b) {
     return __fmul_rn(sqrtf(-2.0f * logf(u1)), cospif(x));
 }
 
+// Two standard normals from one (a, b) word pair, same exactly-representable inputs as normal_f: r cos(pi x), r sin(pi x)
+SRE_DEV void normal2_f(uint32_t a, uint32_t b, float &z0, float &z1) {
+    const float u1 = (float)(2u * (a >> 9) + 1u) * (1.0f / 16777216.0f);
+    const float x = (float)((int32_t)b >> 8) * (1.0f / 8388608.0f);
+    const float r = sqrtf(-2.0f * logf(u1));
+    float sn, cs;
+    sincospif(x, &sn, &cs);
+    z0 = __fmul_rn(r, cs);
+    z1 = __fmul_rn(r, sn);
+}
+
 // DomainParam.sample for one table entry (domain_parameter.py:104-132): float32 draw like torch's default
 // dtype -> clamp -> optional round.  Separate roundings (no FMA contraction): loc + scale * eps.
 SRE_DEV float sample_entry(const sre_distr &d, uint64_t seed, uint64_t env, uint32_t episode, uint32_t entry) {

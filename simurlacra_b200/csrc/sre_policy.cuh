@@ -18,6 +18,8 @@ struct KPolicy {
     const float *weights;  // device, torch layout
     long long n_weights;
     int smem_floats;  // size of the staged (re-laid-out) copy
+    int act_noise;    // SRE_ACT_NOISE_*
+    float noise_scale[SRE_MAX_DA], noise_mean[SRE_MAX_DA];
 };
 
 SRE_DEV float nonlin_f(int kind, float x) {

@@ -233,6 +233,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
             else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
             else linear_forward<DO, DA>(pol, sm_w, of, af);
+            if (pol.act_noise && stepping)
+                add_act_noise<DA>(pol.act_noise, pol.noise_scale, pol.noise_mean, io.seed, genv, episode, (uint32_t)t_ep, af);
 #pragma unroll
             for (int i = 0; i < DA; i++) act[i] = (R)af[i];
         }

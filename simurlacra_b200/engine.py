@@ -132,8 +132,10 @@ def make_distr_table(entries: Sequence[dict]):
 
 
 def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), feats=(), hidden_nonlin: int = 0,
-                output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = 0) -> L.Policy:
+                output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = 0, act_noise: int = 0,
+                act_noise_scale=(), act_noise_mean=()) -> L.Policy:
     p = L.Policy()
+    set_act_noise(p, act_noise, act_noise_scale, act_noise_mean)
     p.kind = kind
     p.n_layers = max(len(sizes) - 1, 0)
     for i, s in enumerate(sizes):
@@ -149,6 +151,16 @@ def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), fea
         p._keep = weights
         p.weights = weights.data_ptr()
         p.n_weights = weights.numel()
+    return p
+
+
+def set_act_noise(p: L.Policy, kind: int, scale=(), mean=()) -> L.Policy:
+    """Step-based exploration fused into the rollout kernel: kind L.ACT_NOISE_NORMAL (scale = std) or
+    L.ACT_NOISE_UNIFORM (scale = halfspan); `mean` is the noise's own mean (train_mean), zeros if empty."""
+    p.act_noise = int(kind)
+    for i in range(L.MAX_DA):
+        p.act_noise_scale[i] = float(scale[i]) if i < len(scale) else 0.0
+        p.act_noise_mean[i] = float(mean[i]) if i < len(mean) else 0.0
     return p
 
 

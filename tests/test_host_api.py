@@ -282,3 +282,59 @@ def test_multi_rank_statistics_allreduce_gloo(tmp_path):
                        capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
+
+
+def test_exploration_strategies_torch_side():
+    """Pyrado/tests/test_exploration.py: noise modules and step-based exploration strategies around a policy."""
+    from simurlacra_b200.exploration import (DiagNormalNoise, NormalActNoiseExplStrat, UniformActNoiseExplStrat,
+                                             UniformNoise)
+
+    env = QBallBalancerSim(dt=0.01)
+    torch.manual_seed(0)
+    pol = FNNPolicy(env.spec, hidden_sizes=[16, 16], hidden_nonlin=torch.tanh)
+    ex = NormalActNoiseExplStrat(pol, std_init=0.5)
+    assert torch.allclose(ex.std, torch.full((2,), 0.5)) and ex.mean is None
+    assert ex.noise.engine_noise() == (L.ACT_NOISE_NORMAL, [0.5, 0.5], [0.0, 0.0])
+    obs = torch.zeros(8)
+    a = ex(obs)
+    assert a.shape == (2,) and not torch.equal(a, pol(obs))
+    acts = torch.stack([ex(obs) for _ in range(4000)])
+    assert abs(float(acts.std(dim=0).mean()) - 0.5) < 0.03 and torch.allclose(acts.mean(dim=0), pol(obs), atol=0.05)
+    ex.std = torch.tensor([1e-9, 2.0])  # the setter clips at std_min (normal_noise.py:118-124)
+    assert torch.allclose(ex.std, torch.tensor([1e-3, 2.0]))
+    ex.reset_expl_params()
+    assert torch.allclose(ex.std, torch.full((2,), 0.5))
+    ent = ex.get_entropy()
+    assert torch.isclose(ent, torch.tensor(0.5 + 0.5 * np.log(2 * np.pi) + 0.5 * np.log(0.5 ** 4), dtype=ent.dtype))
+    ex.noise.adapt(std=torch.tensor([0.1, 0.2]))
+    assert torch.allclose(ex.std, torch.tensor([0.1, 0.2]))
+    with pytest.raises(AssertionError):
+        ex.noise.adapt(mean=torch.zeros(2))  # fixed zero mean
+    with pytest.raises(pyrado.ShapeErr):
+        ex.noise.adapt(std=torch.ones(3))
+    with pytest.raises(pyrado.ValueErr):
+        DiagNormalNoise(noise_dim=2, std_init=-1.0)
+    with pytest.raises(pyrado.TypeErr):
+        DiagNormalNoise(noise_dim=2, std_init="0.1")
+    with pytest.raises(pyrado.ShapeErr):
+        DiagNormalNoise(noise_dim=2, std_init=torch.ones(3))
+    tm = NormalActNoiseExplStrat(pol, std_init=0.1, train_mean=True)
+    tm.noise.adapt(mean=torch.tensor([0.3, -0.3]))
+    assert tm.noise.engine_noise()[2] == pytest.approx([0.3, -0.3])
+    assert set(n for n, _ in tm.named_parameters()) >= {"_noise.log_std", "_noise.mean"}
+    # the wrapper forwards the engine precision to the wrapped policy
+    tm.engine_precision = L.PREC_TF32X3
+    assert pol.engine_precision == L.PREC_TF32X3 and tm.engine_precision == L.PREC_TF32X3
+    un = UniformActNoiseExplStrat(pol, halfspan_init=0.2)
+    acts = torch.stack([un(obs) for _ in range(2000)]) - pol(obs)
+    assert float(acts.abs().max()) <= 0.2 + 1e-6 and float(acts.abs().max()) > 0.19
+    assert torch.allclose(un.get_entropy(), torch.log(torch.tensor([0.4, 0.4])))
+    assert un.noise.engine_noise()[0] == L.ACT_NOISE_UNIFORM
+    with pytest.raises(pyrado.ValueErr):
+        UniformNoise(False, 2, halfspan_init=0.0)
+    # evaluate(): distribution with gradient data for the learner
+    ro = StepSequence(observations=torch.zeros(6, 8), actions=torch.zeros(5, 2), rewards=torch.zeros(5), data_format="torch")
+    dist = tm.evaluate(ro)
+    lp = dist.log_prob(ro.actions).sum()
+    lp.backward()
+    assert tm.noise.log_std.grad is not None and pol.param_grad.abs().sum() > 0
