@@ -32,8 +32,8 @@ import pyrado  # noqa: E402
 from pyrado.environments.pysim.ball_on_beam import BallOnBeamSim  # noqa: E402
 from pyrado.environments.pysim.one_mass_oscillator import OneMassOscillatorSim  # noqa: E402
 from pyrado.environments.pysim.quanser_ball_balancer import QBallBalancerSim  # noqa: E402
-from pyrado.environments.pysim.quanser_cartpole import QCartPoleSwingUpSim  # noqa: E402
-from pyrado.environments.pysim.quanser_qube import QQubeSwingUpSim  # noqa: E402
+from pyrado.environments.pysim.quanser_cartpole import QCartPoleStabSim, QCartPoleSwingUpSim  # noqa: E402
+from pyrado.environments.pysim.quanser_qube import QQubeStabSim, QQubeSwingUpSim  # noqa: E402
 from pyrado.environment_wrappers.action_normalization import ActNormWrapper, ObsActCatWrapper  # noqa: E402
 from pyrado.domain_randomization.default_randomizers import (  # noqa: E402
     create_default_randomizer_bob,
@@ -54,6 +54,11 @@ def make_env(name, **kw):
         return QCartPoleSwingUpSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600),
                                    long=kw.get("long", True), simple_dynamics=kw.get("simple_dynamics", False),
                                    wild_init=kw.get("wild_init", "True"))
+    if name == "qq-st":
+        return QQubeStabSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600))
+    if name == "qcp-st":
+        return QCartPoleStabSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600),
+                                long=kw.get("long", True), simple_dynamics=kw.get("simple_dynamics", False))
     if name == "qbb":
         return QBallBalancerSim(dt=kw.get("dt", 0.01), max_steps=kw.get("max_steps", 500),
                                 simple_dynamics=kw.get("simple_dynamics", False))
@@ -68,6 +73,8 @@ def make_env(name, **kw):
 RANDOMIZERS = {
     "qq-su": create_default_randomizer_qq,
     "qcp-su": create_default_randomizer_qcp,
+    "qq-st": create_default_randomizer_qq,
+    "qcp-st": create_default_randomizer_qcp,
     "qbb": create_default_randomizer_qbb,
     "bob": create_default_randomizer_bob,
     "omo": create_default_randomizer_omo,
@@ -330,7 +337,17 @@ def gen_dr_moments():
     print("  dr moments written")
 
 
+def gen_stab_envs():
+    """the stabilisation variants (other init / state spaces, FinalRewTask on the cart-pole)."""
+    gen_env_trajs("qq-st", n_cases=4)
+    gen_env_trajs("qcp-st", n_cases=4)
+    gen_env_trajs("qcp-st", n_cases=4, simple_dynamics=True)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "stab":  # only the later additions (leaves the earlier files untouched)
+        gen_stab_envs()
+        sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)
     gen_env_trajs("qcp-su", n_cases=6)
@@ -344,5 +361,6 @@ if __name__ == "__main__":
     print("qbb kin"); gen_qbb_kin()
     print("step diff"); gen_step_diff()
     print("dr"); gen_dr_moments()
+    print("stab"); gen_stab_envs()
     sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
     print(f"golden size: {sz / 1e6:.2f} MB")

@@ -17,6 +17,7 @@ _LIB_PATH = osp.join(_HERE, "_build", "libsre_oracle.so")
 QQ, QCP, QBB, BOB, OMO = 0, 1, 2, 3, 4
 KIND_BY_NAME = {"qq-su": QQ, "qcp-su": QCP, "qbb": QBB, "bob": BOB, "omo": OMO}
 F_SIMPLE_DYN = 1
+F_QCP_STAB = 2
 REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2
 FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8, 16
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3
@@ -221,12 +222,12 @@ def policy_forward(pol, obs, n_act):
 class OracleEnv:
     """One environment of the C oracle with the reference's reset/step semantics (fp64)."""
 
-    def __init__(self, kind, dt, max_steps=0, simple_dynamics=False, long_pole=False):
+    def __init__(self, kind, dt, max_steps=0, simple_dynamics=False, long_pole=False, stab=False):
         self.kind = kind
         self.d = dims(kind)
         self._L = lib()
-        self._h = self._L.orc_create(kind, float(dt), int(max_steps), F_SIMPLE_DYN if simple_dynamics else 0,
-                                     int(long_pole))
+        self._h = self._L.orc_create(kind, float(dt), int(max_steps),
+                                     (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0), int(long_pole))
 
     def __del__(self):
         if getattr(self, "_h", None):

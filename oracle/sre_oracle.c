@@ -43,6 +43,7 @@
 
 /* flags */
 #define ORC_F_SIMPLE_DYN 1 /* QCartPole / QBB simple_dynamics=True */
+#define ORC_F_QCP_STAB 2   /* QCartPoleStabSim state space, quanser_cartpole.py:473-489 */
 
 /* reward function kinds: tasks/reward_functions.py:176 (Quadr), :224 (ExpQuadr), :247 (ScaledExpQuadr) */
 #define ORC_REW_QUADR 0
@@ -191,6 +192,12 @@ static void orc_derive(orc_env *e) {
         const double up[4] = {+l_rail / 2.0 - 0.15, +4 * pi, 1 * l_rail, 20 * pi};
         const double lo[4] = {-l_rail / 2.0 + 0.15, -4 * pi, -1 * l_rail, -20 * pi};
         for (int i = 0; i < 4; i++) { e->st_lo[i] = lo[i]; e->st_up[i] = up[i]; }
+        if (e->flags & ORC_F_QCP_STAB) {
+            /* QCartPoleStabSim._create_spaces, quanser_cartpole.py:473-482: stab_thold = 15 deg (:467) */
+            double thold = 15 / 180.0 * pi;
+            e->st_lo[1] = pi - thold; e->st_up[1] = pi + thold;
+            e->st_lo[3] = -2 * pi; e->st_up[3] = +2 * pi;
+        }
         e->act_lo[0] = -6.0; e->act_up[0] = 6.0; /* MAX_ACT_QCP */
     } break;
     case ORC_QBB: {

@@ -130,6 +130,11 @@ template <typename R> struct Env<SRE_QCP, R> {
         const double up[4] = {l_rail / 2.0 - 0.15, 4 * SRE_PI, l_rail, 20 * SRE_PI};
 #pragma unroll
         for (int i = 0; i < 4; i++) { st_lo[i] = (R)(-up[i]); st_up[i] = (R)up[i]; }
+        if (flags & SRE_F_QCP_STAB) {  // QCartPoleStabSim._create_spaces :473-482, stab_thold = 15 deg (:467)
+            const double thold = 15 / 180.0 * SRE_PI;
+            st_lo[1] = (R)(SRE_PI - thold); st_up[1] = (R)(SRE_PI + thold);
+            st_lo[3] = (R)(-2 * SRE_PI); st_up[3] = (R)(2 * SRE_PI);
+        }
         act_lo[0] = (R)-6; act_up[0] = (R)6;  // MAX_ACT_QCP
     }
     // _dynamics :166-230 == _dynamics_diff :360-431.  Returns x_ddot, th_ddot at (th, xd, thd, u) with the carried

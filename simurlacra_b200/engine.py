@@ -83,11 +83,11 @@ def make_task(kind: int, state_des=None, Q=None, R=None, rew_kind=None, min_rew=
 
 def make_cfg(kind: int, dt: float, max_steps: int = 0, dtype=torch.float32, simple_dynamics: bool = False,
              long_pole: bool = False, wild_init: int = 0, task: Optional[L.Task] = None, base_params=None,
-             act_norm: bool = False, noise_std=None, noise_mean=None, init_box=None) -> L.EnvCfg:
+             act_norm: bool = False, noise_std=None, noise_mean=None, init_box=None, flags: int = 0) -> L.EnvCfg:
     cfg = L.EnvCfg()
     cfg.kind = kind
     cfg.dtype = L.F64 if dtype == torch.float64 else L.F32
-    cfg.flags = L.F_SIMPLE_DYN if simple_dynamics else 0
+    cfg.flags = (L.F_SIMPLE_DYN if simple_dynamics else 0) | int(flags)
     cfg.wild_init = wild_init
     cfg.dt = float(dt)
     cfg.max_steps = int(max_steps) if max_steps and np.isfinite(max_steps) else 0

@@ -36,6 +36,7 @@ class Fusion:
 class SimPyEnv(SimEnv):
     kind: int = None           # SRE_* env kind
     _param_names: tuple = ()   # domain parameter names in the order of the C-ABI parameter vector
+    _pass_init_box = False     # True: the class's init space is not the kernel's built-in one -> passed as a box
 
     def __init__(self, dt: float, max_steps: int = pyrado.inf, task_args: Optional[dict] = None, *, num_envs: int = 1,
                  device: Union[str, torch.device, None] = None, dtype: Optional[torch.dtype] = None):
@@ -197,13 +198,13 @@ class SimPyEnv(SimEnv):
         task = L.Task()
         self._task.fill(task)
         init_box = None
-        if self._custom_init_space and type(self._init_space) is BoxSpace:
+        if (self._custom_init_space or self._pass_init_box) and type(self._init_space) is BoxSpace:
             init_box = self._init_space.bounds
         f = fusion or Fusion()
         return E.make_cfg(self.kind, self._dt, self._max_steps, dtype=self._dtype,
                           simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init, task=task,
                           base_params=self.base_param_vector(), act_norm=f.act_norm, noise_std=f.noise_std,
-                          noise_mean=f.noise_mean, init_box=init_box)
+                          noise_mean=f.noise_mean, init_box=init_box, flags=self._flags & ~L.F_SIMPLE_DYN)
 
     def _alloc(self):
         if self._state is None:

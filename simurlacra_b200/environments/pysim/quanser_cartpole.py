@@ -99,3 +99,40 @@ class QCartPoleSwingUpSim(SimPyEnv):
         t = L.Task()
         self._task.fill(t)
         return t
+
+
+class QCartPoleStabSim(QCartPoleSwingUpSim):
+    """Stabilise the pole in the upright position (pyrado/environments/pysim/quanser_cartpole.py:441-500): the cart-pole
+    dynamics of the swing-up env with theta bounded to pi +- 15 deg (leaving it fails the episode), a narrow init
+    space around the upright pose and a quadratic cost with a state- and time-dependent final cost."""
+
+    name: str = "qcp-st"
+    _pass_init_box = True
+
+    def __init__(self, dt: float, max_steps: int = pyrado.inf, task_args: Optional[dict] = None, long: bool = True,
+                 simple_dynamics: bool = True, **kwargs):
+        self.stab_thold = 15 / 180.0 * np.pi  # [rad] failure threshold of the stabilisation task
+        self.max_init_th_offset = 8 / 180.0 * np.pi  # [rad]
+        super().__init__(dt, max_steps, task_args, long, simple_dynamics, wild_init="False", **kwargs)
+        self._flags |= L.F_QCP_STAB
+
+    def _create_spaces(self):  # :473-489
+        super()._create_spaces()
+        l_rail = self._domain_param["rail_length"]
+        min_state = np.array([-l_rail / 2.0 + self._x_buffer, np.pi - self.stab_thold, -l_rail, -2 * np.pi])
+        max_state = np.array([+l_rail / 2.0 - self._x_buffer, np.pi + self.stab_thold, +l_rail, +2 * np.pi])
+        self._state_space = BoxSpace(min_state, max_state, labels=["x", "theta", "x_dot", "theta_dot"])
+        if not self._custom_init_space:
+            max_init = np.array([+0.02, np.pi + self.max_init_th_offset, +0.02, +5 / 180 * np.pi])
+            min_init = np.array([-0.02, np.pi - self.max_init_th_offset, -0.02, -5 / 180 * np.pi])
+            self._init_space = BoxSpace(min_init, max_init, labels=["x", "theta", "x_dot", "theta_dot"])
+
+    def _create_task(self, task_args: dict):  # :491-500
+        from ...tasks.final_reward import FinalRewMode, FinalRewTask
+        from ...tasks.reward_functions import QuadrErrRewFcn
+
+        state_des = np.asarray(task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0])), dtype=np.float64)
+        Q = task_args.get("Q", np.diag([5e-0, 1e1, 1e-2, 1e-2]))
+        R = task_args.get("R", np.diag([1e-3]))
+        return FinalRewTask(RadiallySymmDesStateTask(self.spec, state_des, QuadrErrRewFcn(Q, R), idcs=[1]),
+                            mode=FinalRewMode(state_dependent=True, time_dependent=True))

@@ -40,3 +40,24 @@ class QQubeSwingUpSim(SimPyEnv):
         Q = task_args.get("Q", np.diag([1.0, 1.0, 2e-2, 5e-3]))
         R = task_args.get("R", np.diag([4e-3]))
         return RadiallySymmDesStateTask(self.spec, state_des, ExpQuadrErrRewFcn(Q, R), idcs=[1])
+
+
+class QQubeStabSim(QQubeSwingUpSim):
+    """Stabilise the pendulum at the top (pyrado/environments/pysim/quanser_qube.py:191-229): the Qube's dynamics and
+    state space with an init space around the upright pose (alpha in [175, 185] deg) and a stiffer reward."""
+
+    name: str = "qq-st"
+    _pass_init_box = True
+
+    def _create_spaces(self):  # :203-217
+        super()._create_spaces()
+        if not self._custom_init_space:
+            min_init_state = np.array([-5.0 / 180 * np.pi, 175.0 / 180 * np.pi, 0, 0])
+            max_init_state = np.array([5.0 / 180 * np.pi, 185.0 / 180 * np.pi, 0, 0])
+            self._init_space = BoxSpace(min_init_state, max_init_state, labels=["theta", "alpha", "theta_dot", "alpha_dot"])
+
+    def _create_task(self, task_args: dict):  # :219-229
+        state_des = np.asarray(task_args.get("state_des", np.array([0.0, np.pi, 0.0, 0.0])), dtype=np.float64)
+        Q = task_args.get("Q", np.diag([3.0, 4.0, 2.0, 2.0]))
+        R = task_args.get("R", np.diag([5e-2]))
+        return RadiallySymmDesStateTask(self.spec, state_des, ExpQuadrErrRewFcn(Q, R), idcs=[1])

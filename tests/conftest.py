@@ -42,6 +42,18 @@ ENV_FILES = [
     ("traj_qbb_simple", "qbb", dict(simple_dynamics=True)),
     ("traj_bob", "bob", {}),
     ("traj_omo", "omo", {}),
+    # stabilisation variants (same dynamics, other init / state spaces and tasks)
+    ("traj_qq-st", "qq-su", dict(stab="qq-st")),
+    ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st")),
+    ("traj_qcp-st_simple", "qcp-su", dict(long_pole=True, simple_dynamics=True, stab="qcp-st")),
 ]
+
+# task_args defaults of the stabilisation envs: quanser_qube.py:223-229 (ExpQuadrErrRewFcn), quanser_cartpole.py:491-500
+# (QuadrErrRewFcn inside FinalRewTask(state_dependent, time_dependent)); RadiallySymmDesStateTask idcs=[1] in both
+STAB_TASKS = {
+    "qq-st": dict(state_des=[0.0, np.pi, 0.0, 0.0], Q=np.diag([3.0, 4.0, 2.0, 2.0]), R=np.diag([5e-2]), rew="exp", final=False),
+    "qcp-st": dict(state_des=[0.0, np.pi, 0.0, 0.0], Q=np.diag([5e-0, 1e1, 1e-2, 1e-2]), R=np.diag([1e-3]), rew="quadr",
+                   final=True),
+}
 
 OMO_TASK = dict(state_des=[0.5, 0.0], Q=np.diag([1e1, 1e-2]), R=np.diag([1e-6]))

@@ -17,8 +17,8 @@ from simurlacra_b200.environment_wrappers import (ActNormWrapper, DomainRandWrap
 from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamSim
 from simurlacra_b200.environments.pysim.one_mass_oscillator import OneMassOscillatorSim
 from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
-from simurlacra_b200.environments.pysim.quanser_cartpole import QCartPoleSwingUpSim
-from simurlacra_b200.environments.pysim.quanser_qube import QQubeSwingUpSim
+from simurlacra_b200.environments.pysim.quanser_cartpole import QCartPoleStabSim, QCartPoleSwingUpSim
+from simurlacra_b200.environments.pysim.quanser_qube import QQubeStabSim, QQubeSwingUpSim
 from simurlacra_b200.policies import FeatureStack, FNNPolicy, IdlePolicy, LinearPolicy
 from simurlacra_b200.policies.features import const_feat, identity_feat, squared_feat
 from simurlacra_b200.sampling import ParallelRolloutSampler, StepSequence, rollout
@@ -27,6 +27,11 @@ pytestmark = pytest.mark.gpu
 
 
 def _make_env(kind_name, dt, max_steps, kw, **extra):
+    if kw.get("stab") == "qq-st":
+        return QQubeStabSim(dt=dt, max_steps=max_steps, **extra)
+    if kw.get("stab") == "qcp-st":
+        return QCartPoleStabSim(dt=dt, max_steps=max_steps, long=kw.get("long_pole", False),
+                                simple_dynamics=kw.get("simple_dynamics", False), **extra)
     if kind_name == "qq-su":
         return QQubeSwingUpSim(dt=dt, max_steps=max_steps, **extra)
     if kind_name == "qcp-su":

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import ENV_FILES, OMO_TASK, golden
+from conftest import ENV_FILES, OMO_TASK, STAB_TASKS, golden
 
 pytestmark = pytest.mark.gpu
 
@@ -30,6 +30,13 @@ def _cfg(E, kind_name, dt, max_steps, kw, dtype, **extra):
     task = None
     if kind_name == "omo":
         task = E.make_task(kind, state_des=OMO_TASK["state_des"], Q=OMO_TASK["Q"], R=OMO_TASK["R"])
+    stab = kw.get("stab")
+    if stab:  # QQubeStabSim / QCartPoleStabSim: same kernels, other task (and state space for the cart-pole)
+        t = STAB_TASKS[stab]
+        task = E.make_task(kind, state_des=t["state_des"], Q=t["Q"], R=t["R"],
+                           rew_kind=L.REW_EXP if t["rew"] == "exp" else L.REW_QUADR, radial_idcs=[1],
+                           final_flags=(L.FR_ENABLED | L.FR_STATE_DEP | L.FR_TIME_DEP) if t["final"] else 0)
+        extra = dict(extra, flags=L.F_QCP_STAB if stab == "qcp-st" else 0)
     return E.make_cfg(kind, dt, max_steps, dtype=dtype, simple_dynamics=kw.get("simple_dynamics", False),
                       long_pole=kw.get("long_pole", False), task=task, **extra)
 
@@ -113,7 +120,8 @@ def test_trajectory_fp64_matches_reference(E, fname, kind_name, kw):
 # fp32 over the full horizon: 1e-4 for the non-chaotic envs; the swing-up pendulums are chaotic under the large
 # injected actions of the golden cases, so they are checked over the first 100 steps only
 FP32_TOL = {"traj_omo": (1e-4, None), "traj_bob": (1e-4, None), "traj_qbb": (1e-4, None), "traj_qbb_simple": (1e-4, None),
-            "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100)}
+            "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100),
+            "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50)}
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", ENV_FILES)

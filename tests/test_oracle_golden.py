@@ -8,12 +8,18 @@ All CPU, runs in seconds.
 import numpy as np
 import pytest
 
-from conftest import ENV_FILES, OMO_TASK, golden
+from conftest import ENV_FILES, OMO_TASK, STAB_TASKS, golden
 
 
 def _make(O, kind_name, dt, max_steps, kw):
     kind = O.KIND_BY_NAME[kind_name]
-    e = O.OracleEnv(kind, dt, max_steps, **kw)
+    kw = dict(kw)
+    stab = kw.pop("stab", None)
+    e = O.OracleEnv(kind, dt, max_steps, stab=(stab == "qcp-st"), **kw)
+    if stab:
+        t = STAB_TASKS[stab]
+        e.set_task(t["state_des"], t["Q"], t["R"], O.REW_EXP if t["rew"] == "exp" else O.REW_QUADR, radial_mask=0b10,
+                   final_flags=(O.FR_ENABLED | O.FR_STATE_DEP | O.FR_TIME_DEP) if t["final"] else 0, final_factor=1e3)
     if kind_name == "omo":  # the golden OMO env was built with task_args=dict(state_des=[0.5, 0])
         e.set_task(OMO_TASK["state_des"], OMO_TASK["Q"], OMO_TASK["R"], O.REW_QUADR,
                    final_flags=O.FR_ENABLED | O.FR_ALWAYS_NEG, final_factor=1e3)
