@@ -281,6 +281,18 @@ int sre_task_step_rew(const sre_task *task, int dtype, int ds, int da, double c_
 int sre_policy_forward(const sre_policy *pol, const float *obs, int n_obs, float *act, int n_act, int64_t n,
                        void *stream);
 
+/* ---- post-processing of the record buffer on the device ------------------------------------------------ */
+/* discounted_reverse_cumsum / discounted_value / gae_returns (sampling/step_sequence.py:1049-1116) for every episode
+ * of every lane of a time-major buffer.  rew: real, element (t, n) at rew[t * rew_row_stride + n * rew_lane_stride]
+ * (N*W, W with an offset pointer for the `rew` column of sre_rollout_io.traj; N, 1 for a contiguous [T, N] array);
+ * row_flag [T, N] as written by sre_rollout; values real [T, N] (value estimate of the observation of every row,
+ * closing rows included) or NULL; out_ret real [T, N] discounted return-to-go; out_adv real [T, N] generalised
+ * advantage estimate (NULL iff values is NULL).  Rows without a step (closing / idle) get 0.  A SRE_ROW_TRUNCATED
+ * closing row bootstraps the episode before it from its value estimate. */
+int sre_returns(int dtype, const void *rew, int64_t rew_row_stride, int64_t rew_lane_stride, const uint8_t *row_flag,
+                const void *values, double gamma, double lamb, void *out_ret, void *out_adv, int64_t n_rows,
+                int64_t n_envs, void *stream);
+
 /* ---- persistent-horizon rollout ----------------------------------------------------------------------- */
 int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout_io *io, void *stream);
 /* number of kernels the last sre_rollout call on this thread launched (for bench.py's gpu_launches) */

@@ -337,6 +337,28 @@ def gen_dr_moments():
     print("  dr moments written")
 
 
+def gen_returns():
+    """discounted_value / gae_returns of the unmodified reference (sampling/step_sequence.py:1049-1116) on random
+    complete rollouts (done only at the last step, as rollout() produces them)."""
+    from pyrado.sampling.step_sequence import StepSequence, discounted_value, gae_returns
+
+    rng = np.random.RandomState(77)
+    out = {}
+    cases = [(1, 0.99, 0.95), (2, 0.9, 0.5), (37, 0.99, 0.95), (200, 0.995, 0.97), (64, 1.0, 1.0), (50, 0.0, 0.3)]
+    for c, (n, gamma, lamb) in enumerate(cases):
+        rew = rng.randn(n)
+        val = rng.randn(n + 1)
+        ro = StepSequence(rewards=rew, observations=rng.randn(n + 1, 3), actions=rng.randn(n, 1), values=val,
+                          complete=True)
+        out[f"c{c}_rew"], out[f"c{c}_val"] = rew, val
+        out[f"c{c}_gamma_lamb"] = np.array([gamma, lamb])
+        out[f"c{c}_ret"] = np.asarray(discounted_value(ro, gamma), dtype=np.float64).copy()
+        out[f"c{c}_adv"] = np.asarray(gae_returns(ro, gamma, lamb), dtype=np.float64).copy()
+        print(f"  returns case {c}: n={n} G0={out[f'c{c}_ret'][0]:.6g} A0={out[f'c{c}_adv'][0]:.6g}")
+    out["n_cases"] = np.array(len(cases))
+    np.savez_compressed(osp.join(OUT, "returns_reference.npz"), **out)
+
+
 def gen_stab_envs():
     """the stabilisation variants (other init / state spaces, FinalRewTask on the cart-pole)."""
     gen_env_trajs("qq-st", n_cases=4)
@@ -345,8 +367,8 @@ def gen_stab_envs():
 
 
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "stab":  # only the later additions (leaves the earlier files untouched)
-        gen_stab_envs()
+    if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
+        {"stab": gen_stab_envs, "returns": gen_returns}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)
@@ -362,5 +384,6 @@ if __name__ == "__main__":
     print("step diff"); gen_step_diff()
     print("dr"); gen_dr_moments()
     print("stab"); gen_stab_envs()
+    print("returns"); gen_returns()
     sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
     print(f"golden size: {sz / 1e6:.2f} MB")

@@ -394,3 +394,20 @@ def rollout_batch(kind, dt, max_steps, N, H, *, policy, simple_dynamics=False, l
     out.ret, out.length, out.params_out = res["ret"].ctypes.data, res["length"].ctypes.data, res["params"].ctypes.data
     res["steps"] = lib().orc_rollout_batch(C.byref(cfg), C.byref(policy), N, H, C.byref(out), n_threads)
     return res
+
+
+def returns(rew, flag, gamma, values=None, lamb=0.95):
+    """orc_returns on [T, N] arrays: (ret, adv or None)."""
+    rew = np.ascontiguousarray(rew, dtype=np.float64)
+    flag = np.ascontiguousarray(flag, dtype=np.uint8)
+    T, N = rew.shape
+    ret = np.zeros((T, N))
+    adv = np.zeros((T, N)) if values is not None else None
+    val = np.ascontiguousarray(values, dtype=np.float64) if values is not None else None
+    f = lib().orc_returns
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_long, C.c_long]
+    f(rew.ctypes.data, flag.ctypes.data, val.ctypes.data if val is not None else None, gamma, lamb, ret.ctypes.data,
+      adv.ctypes.data if adv is not None else None, T, N)
+    return ret, adv
+

@@ -1095,3 +1095,47 @@ int orc_num_threads(void) {
     return 1;
 #endif
 }
+
+/* =============================================================================================
+ * Post-processing of rollouts: discounted_reverse_cumsum (sampling/step_sequence.py:1049-1060),
+ * discounted_value (:1063-1072) and gae_returns (:1093-1116), applied to every episode of every lane of a
+ * time-major buffer.  Row flags as written by the engine: 0 step, 1 step with done, 2 closing row of a finished
+ * episode, 3 closing row of a truncated episode, 4 idle.  The reference only knows complete rollouts; a truncated
+ * episode (engine extension) bootstraps from the value estimate of its closing row.
+ * ============================================================================================= */
+void orc_returns(const double *rew, const uint8_t *flag, const double *val, double gamma, double lamb, double *out_ret,
+                 double *out_adv, long T, long N) {
+    for (long n = 0; n < N; n++) {
+        for (long t = 0; t < T; t++) {
+            out_ret[t * N + n] = 0.0;
+            if (out_adv) out_adv[t * N + n] = 0.0;
+        }
+        long t = 0;
+        while (t < T) {
+            if (flag[t * N + n] > 1) { t++; continue; }
+            /* episode = rows a .. b - 1 (steps), row b = closing row (or b == T) */
+            long a = t, b = t;
+            while (b < T && flag[b * N + n] <= 1) b++;
+            int truncated = (b < T && flag[b * N + n] == 3);
+            /* discounted_reverse_cumsum of the rewards: y[i] = x[i] + gamma y[i+1], y[end] = 0 (lfilter zero init) */
+            double y = (truncated && val) ? val[b * N + n] : 0.0;
+            for (long i = b - 1; i >= a; i--) {
+                y = rew[i * N + n] + gamma * y;
+                out_ret[i * N + n] = y;
+            }
+            if (val && out_adv) {
+                /* deltas[i] = r_i + gamma * next_value_i - value_i with next_value = 0 for a done step (:1109-1113) */
+                double c = 0.0;
+                for (long i = b - 1; i >= a; i--) {
+                    int done = flag[i * N + n] == 1;
+                    double nv = done ? 0.0 : ((i + 1 < T) ? val[(i + 1) * N + n] : 0.0);
+                    double delta = rew[i * N + n] + gamma * nv - val[i * N + n];
+                    c = delta + gamma * lamb * c; /* discounted_reverse_cumsum(deltas, gamma * lamb) */
+                    out_adv[i * N + n] = c;
+                }
+            }
+            t = b;
+        }
+    }
+}
+

@@ -150,6 +150,7 @@ SIGNATURES = {
     "sre_policy_forward": (_I, [C.POINTER(Policy), _VP, _I, _VP, _I, _I64, _VP]),
     "sre_rollout": (_I, [C.POINTER(EnvCfg), C.POINTER(Policy), C.POINTER(RolloutIO), _VP]),
     "sre_last_launch_count": (_I, []),
+    "sre_returns": (_I, [_I, _VP, _I64, _I64, _VP, _VP, _D, _D, _VP, _VP, _I64, _I64, _VP]),
     "sre_qcp_diff_forward": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP]),
     "sre_qcp_diff_backward": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP]),
     "sre_qcp_diff_jacobian": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _I64, _VP, _VP]),

@@ -114,6 +114,7 @@ def create_default_randomizer_qbb() -> DomainRandomizer:  # :233-307
     return _from_rows(nom, rows)
 
 
+@default_randomizer(_PYSIM + "quanser_cartpole", "QCartPoleStabSim")
 @default_randomizer(_PYSIM + "quanser_cartpole", "QCartPoleSwingUpSim")
 def create_default_randomizer_qcp() -> DomainRandomizer:  # :310-371 (short-pole nominal values)
     from ..environments.pysim.quanser_cartpole import QCartPoleSwingUpSim
@@ -130,6 +131,7 @@ def create_default_randomizer_qcp() -> DomainRandomizer:  # :310-371 (short-pole
 
 
 @default_randomizer(_PYSIM + "quanser_qube", "QQubeSwingUpSim")
+@default_randomizer(_PYSIM + "quanser_qube", "QQubeStabSim")
 def create_default_randomizer_qq() -> DomainRandomizer:  # :374-416
     from ..environments.pysim.quanser_qube import QQubeSwingUpSim
 

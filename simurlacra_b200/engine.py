@@ -303,6 +303,31 @@ def rollout(cfg, pol: L.Policy, n_envs: int, n_rows: int, *, device, params=None
     return res
 
 
+def returns(rew: torch.Tensor, row_flag: torch.Tensor, gamma: float, values: Optional[torch.Tensor] = None,
+            lamb: float = 0.95):
+    """Discounted returns-to-go (and, with `values`, generalised advantage estimates) of every episode of every lane of
+    a time-major buffer, on the device (sre_returns).  `rew` [T, N] may be a strided view (e.g. the `rew` column of the
+    record buffer); `row_flag` uint8 [T, N]; `values` [T, N] value estimates of every row's observation.
+    Returns (ret [T, N], adv [T, N] or None); rows without a step hold 0."""
+    if rew.dim() != 2 or row_flag.shape != rew.shape or not rew.is_cuda:
+        raise ValueError("rew and row_flag must be CUDA tensors of the same [T, N] shape")
+    if rew.dtype not in (torch.float32, torch.float64):
+        raise ValueError("rew must be float32 or float64")
+    T, N = rew.shape
+    flag = _chk(row_flag.contiguous(), torch.uint8, "row_flag")
+    out_ret = torch.empty(T, N, dtype=rew.dtype, device=rew.device)
+    out_adv = None
+    if values is not None:
+        if values.shape != rew.shape:
+            raise ValueError("values must have the shape of rew")
+        values = _chk(values.to(rew.dtype).contiguous(), rew.dtype, "values")
+        out_adv = torch.empty(T, N, dtype=rew.dtype, device=rew.device)
+    L.check(L.lib().sre_returns(L.F64 if rew.dtype == torch.float64 else L.F32, rew.data_ptr(), rew.stride(0), rew.stride(1),
+                                _ptr(flag), _ptr(values), float(gamma), float(lamb), _ptr(out_ret), _ptr(out_adv), T, N,
+                                _stream()), "sre_returns")
+    return out_ret, out_adv
+
+
 def qcp_diff_forward(cfg, params, s0, act, thdd0=None):
     """act [H, N] inner-env units before the clamp. Returns states [H+1,N,4], thdd [H+1,N], rew [H,N], done [H,N]."""
     dt_ = cfg_dtype(cfg)

@@ -2,3 +2,4 @@
 from .parallel_rollout_sampler import ParallelRolloutSampler  # noqa: F401
 from .rollout import rollout  # noqa: F401
 from .step_sequence import StepSequence, discounted_reverse_cumsum, discounted_value, discounted_values, gae_returns  # noqa: F401
+from . import postprocess  # noqa: F401
