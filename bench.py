@@ -417,6 +417,30 @@ def main():
                                        bytes_per_env_step=lay["width"] * 4 + 1,
                                        env_steps_per_s=sum(float(s[L.STAT_STEPS]) for s in st_q) / t_q)
         del traj, flag
+        # post-processing of a full record set: returns-to-go + GAE over [601, N] contiguous
+        # rewards / values / flags -- a purely HBM-bound pass: 9 B read + 8 B written per row and lane
+        rT = 601
+        g = torch.Generator(device=dev).manual_seed(0)
+        r_rew = torch.randn(rT, qn, device=dev, generator=g)
+        r_val = torch.randn(rT, qn, device=dev, generator=g)
+        r_flag = torch.zeros(rT, qn, dtype=torch.uint8, device=dev)
+        r_flag[200::201] = L.ROW_TERMINAL
+        r_flag[199::201] = L.ROW_DONE
+        o_ret, o_adv = torch.empty_like(r_rew), torch.empty_like(r_rew)
+
+        def ret_step(i):
+            E.returns(r_rew, r_flag, 0.99, values=r_val, lamb=0.95, out_ret=o_ret, out_adv=o_adv)
+
+        for i in range(2):
+            ret_step(i)
+        t_r, _ = timed(ret_step, 3)
+        rb = 3 * rT * qn * 17 / t_r / 1e9
+        extras["roofline_returns"] = dict(bound="hbm", achieved=rb, peak=peaks["hbm_gbs"], unit="GB/s", frac=rb / peaks["hbm_gbs"],
+                                          traffic=(5671760000 + 5001247000) if (rT, qn) == (601, 1 << 20) else None,
+                                          traffic_source="profiles/r01_h_returns_gae_601x1M.txt (dram bytes read + written per launch)", peak_source=f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']})",
+                                          workload=f"sre_returns (discounted returns + GAE), [{rT}, {qn}] f32 rewards / values / "
+                                                   f"flags resident, 17 B per row and lane", rows_per_s=3 * rT * qn / t_r)
+        del r_rew, r_val, r_flag, o_ret, o_adv
 
     if rank == 0:
         line.update(extras)

@@ -304,24 +304,29 @@ def rollout(cfg, pol: L.Policy, n_envs: int, n_rows: int, *, device, params=None
 
 
 def returns(rew: torch.Tensor, row_flag: torch.Tensor, gamma: float, values: Optional[torch.Tensor] = None,
-            lamb: float = 0.95):
+            lamb: float = 0.95, out_ret: Optional[torch.Tensor] = None, out_adv: Optional[torch.Tensor] = None):
     """Discounted returns-to-go (and, with `values`, generalised advantage estimates) of every episode of every lane of
     a time-major buffer, on the device (sre_returns).  `rew` [T, N] may be a strided view (e.g. the `rew` column of the
     record buffer); `row_flag` uint8 [T, N]; `values` [T, N] value estimates of every row's observation.
-    Returns (ret [T, N], adv [T, N] or None); rows without a step hold 0."""
+    Returns (ret [T, N], adv [T, N] or None); rows without a step hold 0.  `out_ret` / `out_adv` reuse caller buffers."""
     if rew.dim() != 2 or row_flag.shape != rew.shape or not rew.is_cuda:
         raise ValueError("rew and row_flag must be CUDA tensors of the same [T, N] shape")
     if rew.dtype not in (torch.float32, torch.float64):
         raise ValueError("rew must be float32 or float64")
     T, N = rew.shape
     flag = _chk(row_flag.contiguous(), torch.uint8, "row_flag")
-    out_ret = torch.empty(T, N, dtype=rew.dtype, device=rew.device)
-    out_adv = None
+    out_ret = torch.empty(T, N, dtype=rew.dtype, device=rew.device) if out_ret is None else _chk(out_ret, rew.dtype, "out_ret")
+    if out_ret.shape != rew.shape:
+        raise ValueError("out_ret must have the shape of rew")
+    if values is None:
+        out_adv = None
     if values is not None:
         if values.shape != rew.shape:
             raise ValueError("values must have the shape of rew")
         values = _chk(values.to(rew.dtype).contiguous(), rew.dtype, "values")
-        out_adv = torch.empty(T, N, dtype=rew.dtype, device=rew.device)
+        out_adv = torch.empty(T, N, dtype=rew.dtype, device=rew.device) if out_adv is None else _chk(out_adv, rew.dtype, "out_adv")
+        if out_adv.shape != rew.shape:
+            raise ValueError("out_adv must have the shape of rew")
     L.check(L.lib().sre_returns(L.F64 if rew.dtype == torch.float64 else L.F32, rew.data_ptr(), rew.stride(0), rew.stride(1),
                                 _ptr(flag), _ptr(values), float(gamma), float(lamb), _ptr(out_ret), _ptr(out_adv), T, N,
                                 _stream()), "sre_returns")

@@ -85,9 +85,9 @@ def main():
     # ---- C3: QCartPoleSwingUp long pole, RK4, 4M envs, uniform DR over pole / cart parameters ----
     nom = QCartPoleSwingUpSim.get_nominal_domain_param(long=True)
     dr = DomainRandomizer(*[UniformDomainParam(name=k, mean=nom[k], halfspan=nom[k] / 5, clip_lo=1e-4)
-                            for k in ("cart_mass", "pole_mass", "pole_length", "rail_length", "pole_damping",
-                                      "combined_damping")])
-    qcp_cfg = E.make_cfg(L.QCP, 1 / 250.0, 600, dtype=torch.float32, long_pole=True, act_norm=True)
+                            for k in ("cart_mass", "pole_mass", "pole_length", "pole_damping", "combined_damping",
+                                      "cart_friction_coeff")])
+    qcp_cfg = E.make_cfg(L.QCP, 1 / 250.0, 600, dtype=torch.float32, long_pole=True, act_norm=True, wild_init=0)
     qcp_distr = dr.table(QCartPoleSwingUpSim._param_names)
     n3 = 1 << (20 if args.quick else 22)
     for prec in (1, 0):
