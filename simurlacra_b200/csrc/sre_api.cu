@@ -32,11 +32,13 @@ int make_kdistr(const sre_env_cfg *cfg, const sre_distr *distr, int n_distr, KDi
                   SRE_MAX_DISTR);
     SRE_CHECK_ARG(n_distr == 0 || distr != nullptr, SRE_E_ARG, "distr is NULL");
     kd.n = n_distr;
+    for (int j = 0; j < SRE_MAX_DP; j++) kd.entry_of_param[j] = -1;
     for (int i = 0; i < n_distr; i++) {
         SRE_CHECK_ARG(distr[i].param_index >= 0 && distr[i].param_index < k_dp[cfg->kind], SRE_E_ARG,
                       "distr[%d].param_index %d outside [0, %d)", i, distr[i].param_index, k_dp[cfg->kind]);
         SRE_CHECK_ARG(distr[i].kind >= 0 && distr[i].kind <= 2, SRE_E_ARG, "distr[%d].kind %d unknown", i, distr[i].kind);
         kd.e[i] = distr[i];
+        kd.entry_of_param[distr[i].param_index] = (signed char)i;  // later entries win, like the sequential loop
     }
     return 0;
 }

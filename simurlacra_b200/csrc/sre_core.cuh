@@ -33,6 +33,7 @@ template <typename R> struct KCfg {
 struct KDistr {
     int n;
     sre_distr e[SRE_MAX_DISTR];
+    signed char entry_of_param[SRE_MAX_DP];  // last table entry that writes parameter j, or -1 (host-filled)
 };
 
 // ------------------------------------------------------------------------------------------------------
@@ -137,11 +138,16 @@ template <int KIND, typename R> struct Lane {
     // reset with a GIVEN init (base.py:166-203); QCP zeroes th_ddot (quanser_cartpole.py:101-106), QBB runs the
     // inverse kinematics (quanser_ball_balancer.py:231-245)
     SRE_DEV void reset(const KCfg<R> &cfg, const R *dp, const R *init, int n_cols) {
+        reset_state(init, n_cols);
+        E::reset_hidden(dp, cfg.flags, s, h);
+    }
+    // the part of reset() that does not depend on the hidden state (the rollout kernel computes QBB's plate angles
+    // warp-cooperatively afterwards)
+    SRE_DEV void reset_state(const R *init, int n_cols) {
         curr_step = 0;
         yielded_final = 0;
         E::state_from_init(init, n_cols, s);
         h[0] = (R)0;
-        E::reset_hidden(dp, cfg.flags, s, h);
     }
 
     // BoxSpace.contains (spaces/box.py:138-167): inclusive bounds; 1 inside, 0 outside, -1 NaN

@@ -37,6 +37,11 @@ SRE_DEV float m_max(float x, float y) { return fmaxf(x, y); }
 SRE_DEV double m_max(double x, double y) { return fmax(x, y); }
 SRE_DEV float m_floor(float x) { return floorf(x); }
 SRE_DEV double m_floor(double x) { return floor(x); }
+SRE_DEV float shfl_r(float v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+SRE_DEV double shfl_r(double v, int src) {
+    const int lo = __shfl_sync(0xffffffffu, __double2loint(v), src), hi = __shfl_sync(0xffffffffu, __double2hiint(v), src);
+    return __hiloint2double(hi, lo);
+}
 template <typename R> SRE_DEV R m_sign(R x) { return (R)((x > (R)0) - (x < (R)0)); }
 template <typename R> SRE_DEV bool m_isnan(R x) { return x != x; }
 

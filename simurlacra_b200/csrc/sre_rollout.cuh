@@ -18,6 +18,9 @@ namespace sre {
 #define SRE_PV_FNN16 16
 #define SRE_PV_FNN32 32
 #define SRE_PV_FNN64 64
+#ifndef SRE_COOP_MAX_LANES
+#define SRE_COOP_MAX_LANES 5  // up to this many restarting lanes of a warp draw their parameters cooperatively
+#endif
 #define SRE_PV_TC 1000    // [do,64,64,da] tanh, hidden layer on the tensor cores, 3 x TF32 (sre_policy_tc.cuh)
 #define SRE_PV_TC1 1001   // the same, single TF32 pass
 
@@ -92,6 +95,11 @@ template <typename R, int PV> struct LaunchShape {
     static constexpr int MIN_BLOCKS = TC ? SRE_TC_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? 2 : 1);
 };
 
+template <int KIND, typename R> SRE_DEV float qbb_plate_ang(R arm_radius, R plate_length, R th_in) {
+    if constexpr (KIND == SRE_QBB) return Env<SRE_QBB, R>::plate_ang(arm_radius, plate_length, th_in);
+    else return 0.f;
+}
+
 template <int KIND, typename R, int PV>
 __global__ void __launch_bounds__((LaunchShape<R, PV>::THREADS), (LaunchShape<R, PV>::MIN_BLOCKS))
 rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDistr distr,
@@ -147,38 +155,94 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         sm_stats[threadIdx.x] = threadIdx.x == SRE_STAT_MIN_RET ? 1e300 : (threadIdx.x == SRE_STAT_MAX_RET ? -1e300 : 0.0);
     __syncthreads();
 
-    auto start_episode = [&]() {
+    // Episode start for the lanes in `mask` (DomainRandWrapperLive.reset + SimPyEnv.reset).  WARP-UNIFORM: every lane
+    // of the warp calls it, `mine` says whether this lane starts an episode.  When only a few lanes restart (the common
+    // case after the synchronous first episode) the other lanes are put to work instead of idling through the
+    // divergent path: lane i draws table entry i of the restarting lane (one Philox block + Box-Muller per warp
+    // instead of distr.n per lane), and QBB's two inverse-kinematics solves of each restarting lane run on two lanes.
+    auto start_episode = [&](bool mine, unsigned mask) {
+        const unsigned FULL = 0xffffffffu;
+        if (mine) {
 #pragma unroll
-        for (int i = 0; i < DP; i++)
-            dp[i] = io.params ? static_cast<const R *>(io.params)[n * DP + i] : cfg.base_params[i];
+            for (int i = 0; i < DP; i++)
+                dp[i] = io.params ? static_cast<const R *>(io.params)[n * DP + i] : cfg.base_params[i];
+        }
+        const int k = __popc(mask);
         // DomainRandWrapperLive.reset (environment_wrappers/domain_randomization.py:141-148)
-        for (int i = 0; i < distr.n; i++) {
-            const float v = sample_entry(distr.e[i], io.seed, genv, episode, (uint32_t)i);
-            const int pi = distr.e[i].param_index;
+        if (distr.n > 0 && k <= SRE_COOP_MAX_LANES) {
+            for (unsigned m = mask; m; m &= m - 1) {
+                const int src = __ffs(m) - 1;
+                const uint32_t g_lo = __shfl_sync(FULL, (uint32_t)genv, src);
+                const uint32_t g_hi = __shfl_sync(FULL, (uint32_t)(genv >> 32), src);
+                const uint32_t ep = __shfl_sync(FULL, episode, src);
+                float v = 0.f;
+                if (lane < distr.n)
+                    v = sample_entry(distr.e[lane], io.seed, ((uint64_t)g_hi << 32) | g_lo, ep, (uint32_t)lane);
 #pragma unroll
-            for (int j = 0; j < DP; j++)
-                if (j == pi) dp[j] = (R)v;  // static register indexing
-        }
-        L.set_params(cfg, dp);
-        if (first_episode && io.params_out) {
+                for (int j = 0; j < DP; j++) {
+                    const int e = distr.entry_of_param[j];  // warp-uniform
+                    if (e >= 0) {
+                        const float vj = __shfl_sync(FULL, v, e);
+                        if (lane == src) dp[j] = (R)vj;
+                    }
+                }
+            }
+        } else if (distr.n > 0 && mine) {
+            for (int i = 0; i < distr.n; i++) {
+                const float v = sample_entry(distr.e[i], io.seed, genv, episode, (uint32_t)i);
+                const int pi = distr.e[i].param_index;
 #pragma unroll
-            for (int i = 0; i < DP; i++) static_cast<R *>(io.params_out)[n * DP + i] = dp[i];
+                for (int j = 0; j < DP; j++)
+                    if (j == pi) dp[j] = (R)v;  // static register indexing
+            }
         }
-        R init[DS];
-        int n_cols = E::DINIT;
-        if (io.init) {
-            n_cols = io.n_init_cols;
+        if (mine) {
+            L.set_params(cfg, dp);
+            if (first_episode && io.params_out) {
 #pragma unroll
-            for (int i = 0; i < DS; i++)
-                if (i < n_cols) init[i] = static_cast<const R *>(io.init)[n * n_cols + i];
-        } else {
-            sample_init<KIND, R>(cfg, dp, io.seed, genv, episode, init);
+                for (int i = 0; i < DP; i++) static_cast<R *>(io.params_out)[n * DP + i] = dp[i];
+            }
+            R init[DS];
+            int n_cols = E::DINIT;
+            if (io.init) {
+                n_cols = io.n_init_cols;
+#pragma unroll
+                for (int i = 0; i < DS; i++)
+                    if (i < n_cols) init[i] = static_cast<const R *>(io.init)[n * n_cols + i];
+            } else {
+                sample_init<KIND, R>(cfg, dp, io.seed, genv, episode, init);
+            }
+            L.reset_state(init, n_cols);
         }
-        L.reset(cfg, dp, init, n_cols);
-        L.observe(obs);
-        t_ep = 0;
-        ret_ep = (R)0;
-        failed_ep = false;
+        if (KIND == SRE_QBB && !(cfg.flags & SRE_F_SIMPLE_DYN)) {
+            // quanser_ball_balancer.py:231-245: plate angles from the inverse kinematics, two 100-iteration solves per
+            // episode start.  Worker lane w serves the (w / 2)-th restarting lane of the chunk, axis w & 1.
+            const R in0 = mine ? dp[4 % DP] : (R)0, in1 = mine ? dp[3 % DP] : (R)0;
+            const R in2 = mine ? L.s[0] + dp[18 % DP] : (R)0, in3 = mine ? L.s[1 % DS] + dp[19 % DP] : (R)0;
+            const int my_rank = __popc(mask & ((1u << lane) - 1u));
+            for (int base = 0; base < k; base += 16) {
+                const int serve = base + (lane >> 1);
+                const unsigned owner = serve < k ? __fns(mask, 0, serve + 1) : 0u;
+                const R ar = shfl_r(in0, (int)owner), pl = shfl_r(in1, (int)owner);
+                const R t0 = shfl_r(in2, (int)owner), t1 = shfl_r(in3, (int)owner);
+                float ang = 0.f;
+                if (serve < k) ang = qbb_plate_ang<KIND, R>(ar, pl, (lane & 1) ? t1 : t0);
+                const int w0 = 2 * (my_rank - base);
+                const float a0 = __shfl_sync(FULL, ang, w0 & 31), a1 = __shfl_sync(FULL, ang, (w0 + 1) & 31);
+                if (mine && my_rank >= base && my_rank < base + 16) {
+                    L.h[0] = (R)a0;
+                    L.h[1 % (NH > 0 ? NH : 1)] = (R)a1;
+                }
+            }
+        } else if (mine) {
+            E::reset_hidden(dp, cfg.flags, L.s, L.h);
+        }
+        if (mine) {
+            L.observe(obs);
+            t_ep = 0;
+            ret_ep = (R)0;
+            failed_ep = false;
+        }
     };
     auto finish_episode = [&](bool complete) {
         if (first_episode) {
@@ -200,7 +264,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
     };
 
-    if (valid) start_episode();
+    start_episode(valid, __ballot_sync(0xffffffffu, valid));
 
     for (long long row = 0; row < T; row++) {
         R rec[W];
@@ -208,6 +272,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         for (int i = 0; i < W; i++) rec[i] = (R)0;
         unsigned char flag = SRE_ROW_IDLE;
 
+        bool restart = false;
         const bool stepping = (lane_state == RUN && row < T - 1);
         const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
         if ((stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
@@ -286,11 +351,15 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             finish_episode(complete);
             if (io.auto_reset && row < T - 1) {
                 episode += 1;
-                start_episode();
+                restart = true;
                 lane_state = RUN;
             } else {
                 lane_state = IDLE;
             }
+        }
+        {
+            const unsigned rs = __ballot_sync(0xffffffffu, restart);
+            if (rs) start_episode(restart, rs);  // the closing row's record is already in `rec`
         }
 
         if (record) {
