@@ -244,22 +244,38 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             failed_ep = false;
         }
     };
-    auto finish_episode = [&](bool complete) {
-        if (first_episode) {
+    // Episode end.  Per lane: the first episode's return / length.  Statistics: WARP-UNIFORM -- the closing lanes' values
+    // are gathered with shuffles, every lane forms the same partial sums and lane 0 issues ONE set of shared-memory
+    // atomics per warp and row (fp64 shared atomics are CAS loops: per-lane updates serialise when lanes close together)
+    auto finish_episodes = [&](bool mine, bool complete, unsigned mask) {
+        if (mine && first_episode) {
             if (io.ret) static_cast<R *>(io.ret)[n] = ret_ep;
             if (io.length) io.length[n] = t_ep;
             first_episode = false;
         }
-        if (io.stats) {
-            atomicAdd(&sm_stats[SRE_STAT_STEPS], (double)t_ep);
-            if (complete) {
-                atomicAdd(&sm_stats[SRE_STAT_EPISODES], 1.0);
-                atomicAdd(&sm_stats[SRE_STAT_SUM_RET], (double)ret_ep);
-                atomicAdd(&sm_stats[SRE_STAT_SUM_RET2], (double)ret_ep * (double)ret_ep);
-                atomicAdd(&sm_stats[SRE_STAT_SUM_LEN], (double)t_ep);
-                if (failed_ep) atomicAdd(&sm_stats[SRE_STAT_FAILED], 1.0);
-                atomic_min_double(&sm_stats[SRE_STAT_MIN_RET], (double)ret_ep);
-                atomic_max_double(&sm_stats[SRE_STAT_MAX_RET], (double)ret_ep);
+        if (!io.stats) return;
+        const unsigned cmask = __ballot_sync(0xffffffffu, mine && complete);
+        const unsigned fmask = __ballot_sync(0xffffffffu, mine && complete && failed_ep);
+        const int steps = __reduce_add_sync(0xffffffffu, mine ? t_ep : 0);
+        const int len = __reduce_add_sync(0xffffffffu, (mine && complete) ? t_ep : 0);
+        double sum = 0.0, sum2 = 0.0, mn = 1e300, mx = -1e300;
+        for (unsigned m = cmask; m; m &= m - 1) {
+            const double r = (double)shfl_r(ret_ep, __ffs(m) - 1);
+            sum += r;
+            sum2 += r * r;
+            mn = fmin(mn, r);
+            mx = fmax(mx, r);
+        }
+        if (lane == 0) {
+            atomicAdd(&sm_stats[SRE_STAT_STEPS], (double)steps);
+            if (cmask) {
+                atomicAdd(&sm_stats[SRE_STAT_EPISODES], (double)__popc(cmask));
+                atomicAdd(&sm_stats[SRE_STAT_SUM_RET], sum);
+                atomicAdd(&sm_stats[SRE_STAT_SUM_RET2], sum2);
+                atomicAdd(&sm_stats[SRE_STAT_SUM_LEN], (double)len);
+                if (fmask) atomicAdd(&sm_stats[SRE_STAT_FAILED], (double)__popc(fmask));
+                atomic_min_double(&sm_stats[SRE_STAT_MIN_RET], mn);
+                atomic_max_double(&sm_stats[SRE_STAT_MAX_RET], mx);
             }
         }
     };
@@ -272,7 +288,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         for (int i = 0; i < W; i++) rec[i] = (R)0;
         unsigned char flag = SRE_ROW_IDLE;
 
-        bool restart = false;
+        bool restart = false, closed = false, closed_complete = false;
         const bool stepping = (lane_state == RUN && row < T - 1);
         const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
         if ((stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
@@ -348,18 +364,27 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             for (int i = 0; i < NH; i++) rec[RC::OFF_HIDDEN + i] = L.h[i];
             const bool complete = (lane_state == CLOSING);
             flag = complete ? SRE_ROW_TERMINAL : SRE_ROW_TRUNCATED;
-            finish_episode(complete);
-            if (io.auto_reset && row < T - 1) {
-                episode += 1;
-                restart = true;
-                lane_state = RUN;
-            } else {
-                lane_state = IDLE;
-            }
+            closed = true;
+            closed_complete = complete;
         }
         {
-            const unsigned rs = __ballot_sync(0xffffffffu, restart);
-            if (rs) start_episode(restart, rs);  // the closing row's record is already in `rec`
+            // warp-uniform tail of the closing rows: statistics, then the next episodes (the closing row's record is
+            // already in `rec`)
+            const unsigned cm = __ballot_sync(0xffffffffu, closed);
+            if (cm) {
+                finish_episodes(closed, closed_complete, cm);
+                if (closed) {
+                    if (io.auto_reset && row < T - 1) {
+                        episode += 1;
+                        restart = true;
+                        lane_state = RUN;
+                    } else {
+                        lane_state = IDLE;
+                    }
+                }
+                const unsigned rs = __ballot_sync(0xffffffffu, restart);
+                if (rs) start_episode(restart, rs);
+            }
         }
 
         if (record) {
