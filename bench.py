@@ -351,7 +351,8 @@ def main():
                                         f"runs at half the bf16 rate",
                             note=f"{passes} tcgen05.mma kind::tf32 pass(es) per 64x64 layer (3xTF32 split keeps fp32-level "
                                  f"accuracy); per env-step only 8192 of {flop} FLOP are GEMM-shaped, the rest (layer 1, "
-                                 f"128 tanh, layer 3, dynamics, sincos, reward) runs on the CUDA cores:                                  f"slots 57% and the MUFU pipe 49% busy, tensor pipe 23% (profiles/r01_i_*), so the "
+                                 f"128 tanh, layer 3, dynamics, sincos, reward) runs on the CUDA cores: ncu shows issue "
+                                 f"slots 57% and the MUFU pipe 49% busy, tensor pipe 23% (profiles/r01_i_*), so the "
                                  f"kernel is CUDA-core/MUFU bound -- see roofline_fp32")
             extras["roofline_fp32"] = fp32_roof
         else:
