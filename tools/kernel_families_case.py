@@ -1,5 +1,5 @@
 """Small end-to-end case that launches every kernel family once (debugging aid; compute-sanitizer is closed on this pool): the (FMA, tcgen05, records, auto-reset,
-exploration noise, QBB cooperative restart), the returns kernel and the adjoint.  python tools/sanitize_case.py"""
+exploration noise, QBB cooperative restart), the returns kernel and the adjoint.  python tools/kernel_families_case.py"""
 import os.path as osp
 import sys
 
@@ -37,4 +37,4 @@ act = torch.ones(50, N, device=dev)
 st, thdd, rew, done = E.qcp_diff_forward(cfg, None, s0, act)
 E.qcp_diff_backward(cfg, None, st, thdd, act, g_rew=torch.ones(50, N, device=dev))
 torch.cuda.synchronize()
-print("sanitize case done")
+print("all kernel families ran")
