@@ -73,6 +73,9 @@ extern "C" {
 #define SRE_POL_IDLE 3    /* policies/feed_forward/dummy.py (IdlePolicy): zero action */
 
 /* sre_policy.precision */
+#define SRE_ENV_ACT_NOISE_NONE 0
+#define SRE_ENV_ACT_NOISE_OUTER 1
+#define SRE_ENV_ACT_NOISE_INNER 2
 #define SRE_ACT_NOISE_NONE 0
 #define SRE_ACT_NOISE_NORMAL 1
 #define SRE_ACT_NOISE_UNIFORM 2
@@ -163,6 +166,17 @@ typedef struct sre_env_cfg {
     int32_t reserved;
     double init_box_lo[SRE_MAX_DS];
     double init_box_up[SRE_MAX_DS];
+    /* ObsNormWrapper._process_obs (environment_wrappers/observation_normalization.py:119-122), applied AFTER the
+     * observation noise: obs = (obs - obs_lb) / (obs_ub - obs_lb) * 2 - 1 with the (overridden) bounds */
+    int32_t obs_norm;
+    /* GaussianActNoiseWrapper._process_act (environment_wrappers/action_noise.py:73-78): act + randn * std + mean.
+     * SRE_ENV_ACT_NOISE_OUTER: the wrapper sits outside ActNormWrapper (noise in normalised units, before the
+     * de-normalisation); SRE_ENV_ACT_NOISE_INNER: inside it (env units).  Philox stream 4, block = step index. */
+    int32_t env_act_noise;
+    double obs_lb[SRE_MAX_DO];
+    double obs_ub[SRE_MAX_DO];
+    double env_act_noise_std[SRE_MAX_DA];
+    double env_act_noise_mean[SRE_MAX_DA];
 } sre_env_cfg;
 
 /* DomainParam (domain_randomization/domain_parameter.py:46): float32 sample -> clamp -> optional round */

@@ -84,6 +84,9 @@ class RolloutCfg(C.Structure):
         ("actions", C.c_void_p),
         ("seed", C.c_uint64), ("env_offset", C.c_uint64), ("episode", C.c_uint32),
         ("stop_on_done", C.c_int),
+        ("obs_norm", C.c_int), ("env_act_noise", C.c_int),
+        ("obs_lb", C.c_double * MAX_DO), ("obs_ub", C.c_double * MAX_DO),
+        ("an_std", C.c_double * MAX_DA), ("an_mean", C.c_double * MAX_DA),
     ]
 
 
@@ -326,11 +329,20 @@ class OracleEnv:
 def rollout_batch(kind, dt, max_steps, N, H, *, policy, simple_dynamics=False, long_pole=False, wild_init=0,
                   task=None, act_norm=False, noise_std=None, noise_mean=None, params=None, distr=None, init=None,
                   init_box=None, actions=None, seed=0, env_offset=0, episode=0, stop_on_done=True, record=True,
-                  n_threads=0):
+                  n_threads=0, stab=False, obs_norm=None, env_act_noise=None):
     """Run N independent rollouts on the CPU oracle. Returns a dict of arrays ([T, N, d] layout) + 'steps'."""
     d = dims(kind)
     cfg = RolloutCfg()
-    cfg.kind, cfg.flags, cfg.long_pole, cfg.wild_init = kind, (F_SIMPLE_DYN if simple_dynamics else 0), int(long_pole), wild_init
+    cfg.kind, cfg.long_pole, cfg.wild_init = kind, int(long_pole), wild_init
+    cfg.flags = (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0)
+    if obs_norm is not None:
+        cfg.obs_norm = 1
+        for i, v in enumerate(np.asarray(obs_norm[0], dtype=np.float64).reshape(-1)): cfg.obs_lb[i] = v
+        for i, v in enumerate(np.asarray(obs_norm[1], dtype=np.float64).reshape(-1)): cfg.obs_ub[i] = v
+    if env_act_noise is not None:
+        cfg.env_act_noise = int(env_act_noise[0])
+        for i, v in enumerate(np.asarray(env_act_noise[1], dtype=np.float64).reshape(-1)): cfg.an_std[i] = v
+        for i, v in enumerate(np.asarray(env_act_noise[2], dtype=np.float64).reshape(-1)): cfg.an_mean[i] = v
     cfg.dt, cfg.max_steps = dt, max_steps
     keep = []
     if task is not None:

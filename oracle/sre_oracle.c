@@ -703,6 +703,7 @@ void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t ou
 #define ORC_STREAM_INIT 1u
 #define ORC_STREAM_OBS_NOISE 2u
 #define ORC_STREAM_ACT_NOISE 3u
+#define ORC_STREAM_ENV_ACT_NOISE 4u
 
 static void orc_rng(uint64_t seed, uint64_t env, uint32_t episode, uint32_t stream, uint32_t block, uint32_t out[4]) {
     uint32_t ctr[4] = {(uint32_t)env, (uint32_t)(env >> 32), episode, (stream << 24) | (block & 0xFFFFFFu)};
@@ -954,6 +955,11 @@ typedef struct {
     const double *actions;     /* [H, N, da] when policy.kind == ACTIONS */
     uint64_t seed; uint64_t env_offset; uint32_t episode;
     int stop_on_done;
+    /* ObsNormWrapper (observation_normalization.py:119-122, after the noise) and GaussianActNoiseWrapper
+     * (action_noise.py:73-78; 1 = outside ActNormWrapper, 2 = inside) */
+    int obs_norm, env_act_noise;
+    double obs_lb[ORC_MAX_DO], obs_ub[ORC_MAX_DO];
+    double an_std[ORC_MAX_DA], an_mean[ORC_MAX_DA];
 } orc_rollout_cfg;
 
 typedef struct {
@@ -1007,6 +1013,8 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
                     for (int j = 0; j < 4 && i + j < dob; j++) obs[i + j] += z[j] * cfg->noise_std[i + j] + cfg->noise_mean[i + j];
                 }
             }
+            if (cfg->obs_norm)
+                for (int i = 0; i < dob; i++) obs[i] = (obs[i] - cfg->obs_lb[i]) / (cfg->obs_ub[i] - cfg->obs_lb[i]) * 2 - 1;
             if (out->obs) memcpy(out->obs + (t * N + n) * dob, obs, sizeof(double) * dob);
             if (out->state) memcpy(out->state + (t * N + n) * ds, e.state, sizeof(double) * ds);
             if (out->hidden && nh) memcpy(out->hidden + (t * N + n) * nh, e.hidden, sizeof(double) * nh);
@@ -1046,9 +1054,25 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
                 }
                 for (int i = 0; i < da; i++) act[i] = (double)af[i];
             }
-            double act_env[ORC_MAX_DA];
-            for (int i = 0; i < da; i++)
-                act_env[i] = cfg->act_norm ? e.act_lo[i] + (act[i] + 1) * (e.act_up[i] - e.act_lo[i]) / 2 : act[i];
+            double act_env[ORC_MAX_DA], an[ORC_MAX_DA] = {0};
+            if (cfg->env_act_noise) {
+                /* noise = randn * std + mean; act + noise (action_noise.py:73-78).  Engine RNG: one block per step,
+                 * the exact-input Box-Muller pair of normal_d */
+                uint32_t x[4];
+                orc_rng(cfg->seed, genv, cfg->episode, ORC_STREAM_ENV_ACT_NOISE, (uint32_t)t, x);
+                double u1 = (double)(2u * (x[0] >> 9) + 1u) * (1.0 / 16777216.0);
+                double ang = (double)((int32_t)x[1] >> 8) * (1.0 / 8388608.0);
+                double r = sqrt(-2.0 * log(u1));
+                double z[2] = {r * cos(M_PI * ang), r * sin(M_PI * ang)};
+                for (int i = 0; i < da; i++) an[i] = z[i] * cfg->an_std[i] + cfg->an_mean[i];
+            }
+            for (int i = 0; i < da; i++) {
+                double a = act[i];
+                if (cfg->env_act_noise == 1) a = a + an[i];
+                if (cfg->act_norm) a = e.act_lo[i] + (a + 1) * (e.act_up[i] - e.act_lo[i]) / 2;
+                if (cfg->env_act_noise == 2) a = a + an[i];
+                act_env[i] = a;
+            }
             double rew;
             if (out->act) memcpy(out->act + (t * N + n) * da, act, sizeof(double) * da);
             if (out->act_app) {
@@ -1078,6 +1102,8 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
                 for (int j = 0; j < 4 && i + j < dob; j++) obs[i + j] += z[j] * cfg->noise_std[i + j] + cfg->noise_mean[i + j];
             }
         }
+        if (cfg->obs_norm)
+            for (int i = 0; i < dob; i++) obs[i] = (obs[i] - cfg->obs_lb[i]) / (cfg->obs_ub[i] - cfg->obs_lb[i]) * 2 - 1;
         if (out->obs) memcpy(out->obs + (t * N + n) * dob, obs, sizeof(double) * dob);
         if (out->state) memcpy(out->state + (t * N + n) * ds, e.state, sizeof(double) * ds);
         if (out->hidden && nh) memcpy(out->hidden + (t * N + n) * nh, e.hidden, sizeof(double) * nh);

@@ -23,6 +23,7 @@ FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3
 PREC_FP32, PREC_TF32X3, PREC_TF32 = 0, 1, 2
 ACT_NOISE_NONE, ACT_NOISE_NORMAL, ACT_NOISE_UNIFORM = 0, 1, 2
+ENV_ACT_NOISE_NONE, ENV_ACT_NOISE_OUTER, ENV_ACT_NOISE_INNER = 0, 1, 2
 FEATS = dict(const=0, identity=1, sign=2, abs=3, squared=4, cubic=5, sin=6, cos=7, sinsin=8, sincos=9)
 DISTR_NORMAL, DISTR_UNIFORM, DISTR_BERNOULLI = 0, 1, 2
 ROW_STEP, ROW_DONE, ROW_TERMINAL, ROW_TRUNCATED, ROW_IDLE = 0, 1, 2, 3, 4
@@ -64,6 +65,12 @@ class EnvCfg(C.Structure):
         ("reserved", C.c_int32),
         ("init_box_lo", C.c_double * MAX_DS),
         ("init_box_up", C.c_double * MAX_DS),
+        ("obs_norm", C.c_int32),
+        ("env_act_noise", C.c_int32),
+        ("obs_lb", C.c_double * MAX_DO),
+        ("obs_ub", C.c_double * MAX_DO),
+        ("env_act_noise_std", C.c_double * MAX_DA),
+        ("env_act_noise_mean", C.c_double * MAX_DA),
     ]
 
 

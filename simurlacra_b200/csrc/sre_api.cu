@@ -23,6 +23,12 @@ int check_cfg(const sre_env_cfg *cfg) {
     SRE_CHECK_ARG(cfg->dt > 0.0 && std::isfinite(cfg->dt), SRE_E_ARG, "dt must be > 0, got %g", cfg->dt);
     SRE_CHECK_ARG(cfg->task.rew_kind >= 0 && cfg->task.rew_kind <= 2, SRE_E_ARG, "unknown reward kind %d",
                   cfg->task.rew_kind);
+    SRE_CHECK_ARG(cfg->env_act_noise >= SRE_ENV_ACT_NOISE_NONE && cfg->env_act_noise <= SRE_ENV_ACT_NOISE_INNER, SRE_E_ARG,
+                  "unknown env_act_noise %d", cfg->env_act_noise);
+    if (cfg->obs_norm)  // observation_normalization.py:69-80: every (overridden) bound must be finite
+        for (int i = 0; i < k_do[cfg->kind]; i++)
+            SRE_CHECK_ARG(std::isfinite(cfg->obs_lb[i]) && std::isfinite(cfg->obs_ub[i]) && cfg->obs_ub[i] > cfg->obs_lb[i],
+                          SRE_E_ARG, "obs_norm bounds of observation %d are [%g, %g]", i, cfg->obs_lb[i], cfg->obs_ub[i]);
     return 0;
 }
 

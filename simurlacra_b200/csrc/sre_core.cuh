@@ -21,12 +21,14 @@ template <typename R> struct KTask {
 };
 
 template <typename R> struct KCfg {
-    int flags, wild_init, act_norm, obs_noise, has_init_box;
+    int flags, wild_init, act_norm, obs_noise, has_init_box, obs_norm, env_act_noise;
     long long max_steps;  // <= 0: inf
     R dt;
     KTask<R> task;
     R base_params[SRE_MAX_DP];
     R noise_std[SRE_MAX_DO], noise_mean[SRE_MAX_DO];
+    R obs_lb[SRE_MAX_DO], obs_span[SRE_MAX_DO];  // ObsNormWrapper: lower bound and (ub - lb)
+    R an_std[SRE_MAX_DA], an_mean[SRE_MAX_DA];    // GaussianActNoiseWrapper
     double init_box_lo[SRE_MAX_DS], init_box_up[SRE_MAX_DS];
 };
 
@@ -241,6 +243,23 @@ SRE_DEV void add_obs_noise(const KCfg<R> &cfg, uint64_t seed, uint64_t env, uint
         for (int j = 0; j < 4; j++)
             if (i + j < DO) obs[i + j] += z[j] * cfg.noise_std[i + j] + cfg.noise_mean[i + j];
     }
+}
+
+// ObsNormWrapper._process_obs (observation_normalization.py:119-122), same operation order
+template <int DO, typename R> SRE_DEV void apply_obs_norm(const KCfg<R> &cfg, R *obs) {
+#pragma unroll
+    for (int i = 0; i < DO; i++) obs[i] = (obs[i] - cfg.obs_lb[i]) / cfg.obs_span[i] * (R)2 - (R)1;
+}
+
+// GaussianActNoiseWrapper._process_act (action_noise.py:73-78): act + (randn * std + mean) in the working type
+template <int DA, typename R>
+SRE_DEV void add_env_act_noise(const KCfg<R> &cfg, uint64_t seed, uint64_t env, uint32_t episode, uint32_t t, R *act) {
+    static_assert(DA <= 2, "one Philox block carries the noise of at most two action dimensions");
+    const u32x4 x = rng_block(seed, env, episode, SRE_STREAM_ENV_ACT_NOISE, t);
+    R z[2];
+    normal2_r(x.x, x.y, z[0], z[1]);
+#pragma unroll
+    for (int i = 0; i < DA; i++) act[i] = act[i] + (z[i] * cfg.an_std[i] + cfg.an_mean[i]);
 }
 
 // StochasticActionExplStrat.forward (exploration/stochastic_action.py:68-94): act = dist(policy(obs) + mean).rsample() in

@@ -53,6 +53,7 @@ template <typename R> SRE_DEV bool m_isnan(R x) { return x != x; }
 #define SRE_STREAM_INIT 1u
 #define SRE_STREAM_OBS_NOISE 2u
 #define SRE_STREAM_ACT_NOISE 3u
+#define SRE_STREAM_ENV_ACT_NOISE 4u
 
 struct u32x4 {
     uint32_t x, y, z, w;
@@ -100,6 +101,18 @@ SRE_DEV void normal2_f(uint32_t a, uint32_t b, float &z0, float &z1) {
     sincospif(x, &sn, &cs);
     z0 = __fmul_rn(r, cs);
     z1 = __fmul_rn(r, sn);
+}
+
+// the same pair in the working type: float32 math in the production build, fp64 in the verification build
+SRE_DEV void normal2_r(uint32_t a, uint32_t b, float &z0, float &z1) { normal2_f(a, b, z0, z1); }
+SRE_DEV void normal2_r(uint32_t a, uint32_t b, double &z0, double &z1) {
+    const double u1 = (double)(2u * (a >> 9) + 1u) * (1.0 / 16777216.0);
+    const double x = (double)((int32_t)b >> 8) * (1.0 / 8388608.0);
+    const double r = sqrt(-2.0 * log(u1));
+    double sn, cs;
+    sincospi(x, &sn, &cs);
+    z0 = r * cs;
+    z1 = r * sn;
 }
 
 // DomainParam.sample for one table entry (domain_parameter.py:104-132): float32 draw like torch's default

@@ -46,6 +46,16 @@ template <typename R> inline void make_kcfg(const sre_env_cfg &c, KCfg<R> &k) {
     k.act_norm = c.act_norm;
     k.obs_noise = c.obs_noise;
     k.has_init_box = c.has_init_box;
+    k.obs_norm = c.obs_norm;
+    k.env_act_noise = c.env_act_noise;
+    for (int i = 0; i < SRE_MAX_DO; i++) {
+        k.obs_lb[i] = (R)c.obs_lb[i];
+        k.obs_span[i] = (R)(c.obs_ub[i] - c.obs_lb[i]);
+    }
+    for (int i = 0; i < SRE_MAX_DA; i++) {
+        k.an_std[i] = (R)c.env_act_noise_std[i];
+        k.an_mean[i] = (R)c.env_act_noise_mean[i];
+    }
     k.max_steps = c.max_steps;
     k.dt = (R)c.dt;
     bool diag = true;

@@ -292,6 +292,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         const bool stepping = (lane_state == RUN && row < T - 1);
         const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
         if ((stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
+        if ((stepping || closing) && cfg.obs_norm) apply_obs_norm<DO, R>(cfg, obs);
         // ---- policy (float32).  The tiled FNN is warp-cooperative, so it runs outside the per-lane branches ----
         R act[DA];
         if (PV == SRE_PV_ACTIONS) {
@@ -323,8 +324,17 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             // ---- wrappers: ActNormWrapper._process_act (action_normalization.py:69-75) ----
             R act_env[DA];
 #pragma unroll
+            for (int i = 0; i < DA; i++) act_env[i] = act[i];
+            // GaussianActNoiseWrapper outside / inside ActNormWrapper (the recorded action stays the policy's)
+            if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER)
+                add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
+#pragma unroll
+            for (int i = 0; i < DA; i++)
+                if (cfg.act_norm) act_env[i] = L.act_lo[i] + (act_env[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2;
+            if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER)
+                add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
+#pragma unroll
             for (int i = 0; i < DA; i++) {
-                act_env[i] = cfg.act_norm ? L.act_lo[i] + (act[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2 : act[i];
                 if (m_isnan(act[i])) status |= SRE_ST_NAN_ACT;
                 // rollout.py:244 env.limit_act(act): through ActNormWrapper the NORMALISED action is clipped to [-1, 1]
                 const R lo = cfg.act_norm ? (R)-1 : L.act_lo[i], up = cfg.act_norm ? (R)1 : L.act_up[i];

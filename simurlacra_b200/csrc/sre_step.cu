@@ -82,6 +82,7 @@ __global__ void reset_kernel(const __grid_constant__ KCfg<R> cfg, const R *param
         R o[E::DO];
         L.observe(o);
         if (cfg.obs_noise) add_obs_noise<E::DO, R>(cfg, seed, env_offset + (unsigned long long)n, episode, 0u, o);
+        if (cfg.obs_norm) apply_obs_norm<E::DO, R>(cfg, o);
 #pragma unroll
         for (int i = 0; i < E::DO; i++) obs[n * E::DO + i] = o[i];
     }
@@ -112,8 +113,14 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     for (int i = 0; i < E::DA; i++) {
         const R v = act[n * E::DA + i];
         if (m_isnan(v)) st |= SRE_ST_NAN_ACT;
-        a[i] = cfg.act_norm ? L.act_lo[i] + (v + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2 : v;
+        a[i] = v;
     }
+    const unsigned long long genv = env_offset + (unsigned long long)n;
+    if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER) add_env_act_noise<E::DA, R>(cfg, seed, genv, episode, (uint32_t)L.curr_step, a);
+#pragma unroll
+    for (int i = 0; i < E::DA; i++)
+        if (cfg.act_norm) a[i] = L.act_lo[i] + (a[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2;
+    if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER) add_env_act_noise<E::DA, R>(cfg, seed, genv, episode, (uint32_t)L.curr_step, a);
     R r;
     int inside;
     R o[E::DO];
@@ -128,6 +135,7 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     L.observe(o);
     if (cfg.obs_noise)
         add_obs_noise<E::DO, R>(cfg, seed, env_offset + (unsigned long long)n, episode, (uint32_t)L.curr_step, o);
+    if (cfg.obs_norm) apply_obs_norm<E::DO, R>(cfg, o);
 #pragma unroll
     for (int i = 0; i < E::DO; i++) obs[n * E::DO + i] = o[i];
     rew[n] = r;

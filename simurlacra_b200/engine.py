@@ -83,7 +83,10 @@ def make_task(kind: int, state_des=None, Q=None, R=None, rew_kind=None, min_rew=
 
 def make_cfg(kind: int, dt: float, max_steps: int = 0, dtype=torch.float32, simple_dynamics: bool = False,
              long_pole: bool = False, wild_init: int = 0, task: Optional[L.Task] = None, base_params=None,
-             act_norm: bool = False, noise_std=None, noise_mean=None, init_box=None, flags: int = 0) -> L.EnvCfg:
+             act_norm: bool = False, noise_std=None, noise_mean=None, init_box=None, flags: int = 0,
+             obs_norm=None, env_act_noise=None) -> L.EnvCfg:
+    """`obs_norm` = (lb, ub) of ObsNormWrapper; `env_act_noise` = (position, std, mean) of GaussianActNoiseWrapper with
+    position L.ENV_ACT_NOISE_OUTER (outside ActNormWrapper) or L.ENV_ACT_NOISE_INNER."""
     cfg = L.EnvCfg()
     cfg.kind = kind
     cfg.dtype = L.F64 if dtype == torch.float64 else L.F32
@@ -103,6 +106,18 @@ def make_cfg(kind: int, dt: float, max_steps: int = 0, dtype=torch.float32, simp
         if noise_mean is not None:
             for i, v in enumerate(np.asarray(noise_mean, dtype=np.float64).reshape(-1)):
                 cfg.noise_mean[i] = v
+    if obs_norm is not None:
+        cfg.obs_norm = 1
+        for i, v in enumerate(np.asarray(obs_norm[0], dtype=np.float64).reshape(-1)):
+            cfg.obs_lb[i] = v
+        for i, v in enumerate(np.asarray(obs_norm[1], dtype=np.float64).reshape(-1)):
+            cfg.obs_ub[i] = v
+    if env_act_noise is not None:
+        cfg.env_act_noise = int(env_act_noise[0])
+        for i, v in enumerate(np.asarray(env_act_noise[1], dtype=np.float64).reshape(-1)):
+            cfg.env_act_noise_std[i] = v
+        for i, v in enumerate(np.asarray(env_act_noise[2], dtype=np.float64).reshape(-1)):
+            cfg.env_act_noise_mean[i] = v
     if init_box is not None:
         cfg.has_init_box = 1
         for i, v in enumerate(np.asarray(init_box[0], dtype=np.float64).reshape(-1)):

@@ -33,7 +33,10 @@ class ActNormWrapper(EnvWrapperAct):
     _fusable = True
 
     def _fuse(self, fusion, below_alters_act, below_alters_obs) -> bool:
-        if below_alters_act:
+        from .action_noise import GaussianActNoiseWrapper
+
+        # a fused GaussianActNoiseWrapper may sit below (noise in env units); anything else runs on the data
+        if any(w._alters_act and type(w) is not GaussianActNoiseWrapper for w in self._below()):
             return False
         fusion.act_norm = True
         return True

@@ -31,6 +31,8 @@ class Fusion:
         self.act_norm = False
         self.noise_std = None
         self.noise_mean = None
+        self.obs_norm = None        # (lb, ub) of an ObsNormWrapper
+        self.env_act_noise = None   # (position, std, mean) of a GaussianActNoiseWrapper
 
 
 class SimPyEnv(SimEnv):
@@ -204,7 +206,8 @@ class SimPyEnv(SimEnv):
         return E.make_cfg(self.kind, self._dt, self._max_steps, dtype=self._dtype,
                           simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init, task=task,
                           base_params=self.base_param_vector(), act_norm=f.act_norm, noise_std=f.noise_std,
-                          noise_mean=f.noise_mean, init_box=init_box, flags=self._flags & ~L.F_SIMPLE_DYN)
+                          noise_mean=f.noise_mean, init_box=init_box, flags=self._flags & ~L.F_SIMPLE_DYN,
+                          obs_norm=f.obs_norm, env_act_noise=f.env_act_noise)
 
     def _alloc(self):
         if self._state is None:

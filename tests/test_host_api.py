@@ -338,3 +338,45 @@ def test_exploration_strategies_torch_side():
     lp = dist.log_prob(ro.actions).sum()
     lp.backward()
     assert tm.noise.log_std.grad is not None and pol.param_grad.abs().sum() > 0
+
+
+def test_obs_norm_and_act_noise_wrappers_host_side():
+    """Pyrado/tests/test_environment_wrappers.py (ObsNormWrapper, GaussianActNoiseWrapper): bounds handling, spaces,
+    domain-parameter entries, and where the wrappers fuse into the kernels."""
+    from simurlacra_b200.environment_wrappers import GaussianActNoiseWrapper, ObsNormWrapper
+
+    qq = QQubeSwingUpSim(dt=0.01)
+    on = ObsNormWrapper(qq)
+    np.testing.assert_array_equal(on.obs_space.bound_lo, -np.ones(6))
+    lb, ub = qq.obs_space.bounds
+    x = np.array([0.5, -0.5, 1.0, -1.0, 10.0, -62.0])
+    np.testing.assert_allclose(on._process_obs(x), (x - lb) / (ub - lb) * 2 - 1)
+    t = on._process_obs(torch.as_tensor(x)[None].repeat(3, 1))
+    assert t.shape == (3, 6) and torch.allclose(t[0], torch.as_tensor(on._process_obs(x)))
+    qcp = QCartPoleSwingUpSim(dt=0.01)
+    with pytest.raises(pyrado.ValueErr):
+        ObsNormWrapper(qcp)  # unbounded velocities (observation_normalization.py:69-80)
+    with pytest.raises(pyrado.ValueErr):
+        ObsNormWrapper(qcp, explicit_lb={"x_dot": -5.0}, explicit_ub={"x_dot": 5.0, "theta_dot": 20.0})
+    ok = ObsNormWrapper(qcp, explicit_lb={"x_dot": -5.0, "theta_dot": -20.0}, explicit_ub={"x_dot": 5.0, "theta_dot": 20.0})
+    assert ok.ov_ub[3] == 5.0 and ok.ov_lb[4] == -20.0 and ok.ov_ub[0] == qcp.obs_space.bound_up[0]
+    an = GaussianActNoiseWrapper(ActNormWrapper(qq), noise_std=[0.1])
+    assert an._mean.shape == (1,) and an.act_space.bound_up[0] == 1.0
+    with pytest.raises(pyrado.ShapeErr):
+        GaussianActNoiseWrapper(qq, noise_std=[0.1, 0.2])
+    dp = an.domain_param
+    assert dp["act_noise_std"][0] == 0.1 and dp["act_noise_mean"][0] == 0.0
+    an.domain_param = dict(act_noise_std=np.array([0.3]))
+    assert an._std[0] == 0.3
+    samples = np.stack([an._process_act(np.zeros(1)) for _ in range(4000)])
+    assert abs(samples.std() - 0.3) < 0.02 and abs(samples.mean()) < 0.02
+    # fusion: noise outside / inside ActNorm, ObsNorm above the observation noise; everything else takes the generic path
+    cc = compile_chain(ObsNormWrapper(GaussianObsNoiseWrapper(an, noise_std=0.1 * np.ones(6))))
+    assert cc.fusion.act_norm and cc.fusion.env_act_noise[0] == L.ENV_ACT_NOISE_OUTER and cc.fusion.obs_norm is not None
+    cfg = cc.sim._make_cfg(cc.fusion)
+    assert cfg.obs_norm == 1 and cfg.env_act_noise == L.ENV_ACT_NOISE_OUTER and cfg.env_act_noise_std[0] == 0.3
+    inner = compile_chain(ActNormWrapper(GaussianActNoiseWrapper(QQubeSwingUpSim(dt=0.01), noise_std=[0.2])))
+    assert inner.fusion.env_act_noise[0] == L.ENV_ACT_NOISE_INNER and inner.fusion.act_norm
+    assert compile_chain(GaussianObsNoiseWrapper(ObsNormWrapper(QQubeSwingUpSim(dt=0.01)), noise_std=np.ones(6))) is None
+    assert compile_chain(GaussianActNoiseWrapper(GaussianActNoiseWrapper(QQubeSwingUpSim(dt=0.01), noise_std=[0.2]),
+                                                 noise_std=[0.2])) is None
