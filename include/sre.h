@@ -35,7 +35,8 @@ extern "C" {
 #define SRE_QBB 2 /* QBallBalancerSim      quanser_ball_balancer.py:50 */
 #define SRE_BOB 3 /* BallOnBeamSim         ball_on_beam.py:41 */
 #define SRE_OMO 4 /* OneMassOscillatorSim  one_mass_oscillator.py:43 */
-#define SRE_N_KINDS 5
+#define SRE_PEND 5 /* PendulumSim           pendulum.py:43 */
+#define SRE_N_KINDS 6
 
 #define SRE_F32 0
 #define SRE_F64 1

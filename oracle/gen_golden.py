@@ -31,6 +31,7 @@ import torch  # noqa: E402
 import pyrado  # noqa: E402
 from pyrado.environments.pysim.ball_on_beam import BallOnBeamSim  # noqa: E402
 from pyrado.environments.pysim.one_mass_oscillator import OneMassOscillatorSim  # noqa: E402
+from pyrado.environments.pysim.pendulum import PendulumSim  # noqa: E402
 from pyrado.environments.pysim.quanser_ball_balancer import QBallBalancerSim  # noqa: E402
 from pyrado.environments.pysim.quanser_cartpole import QCartPoleStabSim, QCartPoleSwingUpSim  # noqa: E402
 from pyrado.environments.pysim.quanser_qube import QQubeStabSim, QQubeSwingUpSim  # noqa: E402
@@ -38,6 +39,7 @@ from pyrado.environment_wrappers.action_normalization import ActNormWrapper, Obs
 from pyrado.domain_randomization.default_randomizers import (  # noqa: E402
     create_default_randomizer_bob,
     create_default_randomizer_omo,
+    create_default_randomizer_pend,
     create_default_randomizer_qbb,
     create_default_randomizer_qcp,
     create_default_randomizer_qq,
@@ -54,6 +56,9 @@ def make_env(name, **kw):
         return QCartPoleSwingUpSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600),
                                    long=kw.get("long", True), simple_dynamics=kw.get("simple_dynamics", False),
                                    wild_init=kw.get("wild_init", "True"))
+    if name == "pend":
+        return PendulumSim(dt=kw.get("dt", 1 / 50.0), max_steps=kw.get("max_steps", 400),
+                           init_state=kw.get("init_state", np.array([0.3, -0.2])))
     if name == "qq-st":
         return QQubeStabSim(dt=kw.get("dt", 1 / 250.0), max_steps=kw.get("max_steps", 600))
     if name == "qcp-st":
@@ -73,6 +78,7 @@ def make_env(name, **kw):
 RANDOMIZERS = {
     "qq-su": create_default_randomizer_qq,
     "qcp-su": create_default_randomizer_qcp,
+    "pend": create_default_randomizer_pend,
     "qq-st": create_default_randomizer_qq,
     "qcp-st": create_default_randomizer_qcp,
     "qbb": create_default_randomizer_qbb,
@@ -368,7 +374,7 @@ def gen_stab_envs():
 
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
-        {"stab": gen_stab_envs, "returns": gen_returns}[sys.argv[1]]()
+        {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6)}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)
@@ -385,5 +391,6 @@ if __name__ == "__main__":
     print("dr"); gen_dr_moments()
     print("stab"); gen_stab_envs()
     print("returns"); gen_returns()
+    print("pend"); gen_env_trajs("pend", n_cases=6)
     sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
     print(f"golden size: {sz / 1e6:.2f} MB")

@@ -14,8 +14,8 @@ import numpy as np
 _HERE = osp.dirname(osp.abspath(__file__))
 _LIB_PATH = osp.join(_HERE, "_build", "libsre_oracle.so")
 
-QQ, QCP, QBB, BOB, OMO = 0, 1, 2, 3, 4
-KIND_BY_NAME = {"qq-su": QQ, "qcp-su": QCP, "qbb": QBB, "bob": BOB, "omo": OMO}
+QQ, QCP, QBB, BOB, OMO, PEND = 0, 1, 2, 3, 4, 5
+KIND_BY_NAME = {"qq-su": QQ, "qcp-su": QCP, "qbb": QBB, "bob": BOB, "omo": OMO, "pend": PEND}
 F_SIMPLE_DYN = 1
 F_QCP_STAB = 2
 REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2

@@ -34,6 +34,7 @@
 #define ORC_QBB 2
 #define ORC_BOB 3
 #define ORC_OMO 4
+#define ORC_PEND 5
 
 #define ORC_MAX_DS 8
 #define ORC_MAX_DO 8
@@ -57,12 +58,12 @@
 #define ORC_FR_ALWAYS_POS 8
 #define ORC_FR_ALWAYS_NEG 16
 
-static const int k_ds[5] = {4, 4, 8, 4, 2};
-static const int k_do[5] = {6, 5, 8, 4, 2};
-static const int k_da[5] = {1, 1, 2, 1, 1};
-static const int k_dp[5] = {11, 17, 20, 8, 3};
-static const int k_nh[5] = {0, 1, 2, 0, 0};
-static const int k_dinit[5] = {4, 4, 4, 4, 2};
+static const int k_ds[6] = {4, 4, 8, 4, 2, 2};
+static const int k_do[6] = {6, 5, 8, 4, 2, 3};
+static const int k_da[6] = {1, 1, 2, 1, 1, 1};
+static const int k_dp[6] = {11, 17, 20, 8, 3, 5};
+static const int k_nh[6] = {0, 1, 2, 0, 0, 0};
+static const int k_dinit[6] = {4, 4, 4, 4, 2, 2};
 
 typedef struct {
     int kind, flags;
@@ -130,6 +131,10 @@ void orc_nominal_params(int kind, int long_pole, double *dp) {
     } break;
     case ORC_OMO: {
         const double v[3] = {1.0, 30.0, 0.5};
+        memcpy(dp, v, sizeof v);
+    } break;
+    case ORC_PEND: { /* pendulum.py:96-104 */
+        const double v[5] = {9.81, 1.0, 1.0, 0.05, 3.5};
         memcpy(dp, v, sizeof v);
     } break;
     }
@@ -236,6 +241,11 @@ static void orc_derive(orc_env *e) {
         e->st_lo[0] = -1.0; e->st_up[0] = 1.0; e->st_lo[1] = -10.0; e->st_up[1] = 10.0;
         e->act_lo[0] = -1.0 * k; e->act_up[0] = 1.0 * k;
     } break;
+    case ORC_PEND: {
+        /* pendulum.py:66-74: max_state = [4 pi, 4 pi], act bound = torque_thold */
+        e->st_lo[0] = -4 * pi; e->st_up[0] = 4 * pi; e->st_lo[1] = -4 * pi; e->st_up[1] = 4 * pi;
+        e->act_lo[0] = -p[4]; e->act_up[0] = p[4];
+    } break;
     }
     orc_update_cmax(e);
 }
@@ -266,6 +276,9 @@ static void orc_default_task(orc_env *e) {
     case ORC_OMO:
         q[0] = 1e1; q[1] = 1e-2; r[0] = 1e-6; e->rew_kind = ORC_REW_QUADR;
         e->final_flags = ORC_FR_ENABLED | ORC_FR_ALWAYS_NEG; e->final_factor = 1e3; break;
+    case ORC_PEND: /* pendulum.py:82-88: RadiallySymmDesStateTask(..., idcs=[1]) as the reference has it */
+        e->state_des[0] = M_PI; q[0] = 1e-0; q[1] = 1e-3; r[0] = 1e-2;
+        e->rew_kind = ORC_REW_EXP; e->radial_mask = 1u << 1; break;
     }
     for (int i = 0; i < ds; i++) e->Q[i * ds + i] = q[i];
     for (int i = 0; i < da; i++) e->R[i * da + i] = r[i];
@@ -334,6 +347,9 @@ void orc_observe(const orc_env *e, const double *s, double *obs) {
         break;
     case ORC_QCP:
         obs[0] = s[0]; obs[1] = sin(s[1]); obs[2] = cos(s[1]); obs[3] = s[2]; obs[4] = s[3];
+        break;
+    case ORC_PEND: /* pendulum.py:93-94 */
+        obs[0] = sin(s[0]); obs[1] = cos(s[0]); obs[2] = s[1];
         break;
     default:
         memcpy(obs, s, sizeof(double) * k_ds[e->kind]);
@@ -620,6 +636,16 @@ static void omo_step(orc_env *e, double act) {
     s[1] = s[1] + sd1 * e->dt;
 }
 
+/* pendulum.py:106-122: rod pendulum, symplectic Euler (velocity first) */
+static void pend_step(orc_env *e, double act) {
+    double g = e->dp[0], m = e->dp[1], l = e->dp[2], d = e->dp[3];
+    double *s = e->state;
+    double th = s[0], th_dot = s[1];
+    double th_ddot = (act - m * g * l / 2.0 * sin(th) - d * th_dot) / (m * (l * l) / 3.0);
+    s[1] += th_ddot * e->dt;
+    s[0] += s[1] * e->dt;
+}
+
 /* Env.limit_act -> BoxSpace.project_to, environments/base.py:215-222, spaces/box.py:180-184 */
 void orc_limit_act(const orc_env *e, const double *act, double *out) {
     for (int i = 0; i < k_da[e->kind]; i++) out[i] = fmin(fmax(act[i], e->act_lo[i]), e->act_up[i]);
@@ -640,6 +666,7 @@ int orc_step(orc_env *e, const double *act, double *obs, double *rew) {
     case ORC_QBB: qbb_step(e, a); break;
     case ORC_BOB: bob_step(e, a[0]); break;
     case ORC_OMO: omo_step(e, a[0]); break;
+    case ORC_PEND: pend_step(e, a[0]); break;
     }
     e->curr_step += 1;
     int inside = orc_contains(e->state, e->st_lo, e->st_up, k_ds[e->kind]);
@@ -818,6 +845,9 @@ void orc_sample_init(const orc_env *e, int wild_init, const double *box_lo, cons
         } break;
         case ORC_OMO:
             lo[0] = -0.75 * 1.0; up[0] = -0.65 * 1.0; lo[1] = -0.01 * 10.0; up[1] = +0.01 * 10.0;
+            break;
+        case ORC_PEND: /* SingularStateSpace(init_state = zeros), pendulum.py:75 */
+            lo[0] = up[0] = 0.0; lo[1] = up[1] = 0.0;
             break;
         }
     }

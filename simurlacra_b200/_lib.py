@@ -13,7 +13,7 @@ LIB_PATH = osp.join(_HERE, "lib", "libsre_b200.so")
 CSRC_DIR = osp.join(_HERE, "csrc")
 
 # ---- constants (include/sre.h) ----
-QQ, QCP, QBB, BOB, OMO = 0, 1, 2, 3, 4
+QQ, QCP, QBB, BOB, OMO, PEND = 0, 1, 2, 3, 4, 5
 F32, F64 = 0, 1
 MAX_DS, MAX_DO, MAX_DA, MAX_DP, MAX_NH, MAX_DISTR, MAX_LAYERS, MAX_WIDTH, MAX_FEATS = 8, 8, 2, 20, 2, 32, 8, 128, 12
 F_SIMPLE_DYN = 1

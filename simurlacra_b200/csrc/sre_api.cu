@@ -181,8 +181,12 @@ int sre_nominal_params(int kind, int long_pole, double *dp) {
         const double v[8] = {9.81, 0.5, 0.1, 3.0, 2.0, 0.1, 0.05, 0.0};
         memcpy(dp, v, sizeof v);
     } break;
-    default: {  // one_mass_oscillator.py:81-87
+    case SRE_OMO: {  // one_mass_oscillator.py:81-87
         const double v[3] = {1.0, 30.0, 0.5};
+        memcpy(dp, v, sizeof v);
+    } break;
+    default: {  // pendulum.py:96-104
+        const double v[5] = {9.81, 1.0, 1.0, 0.05, 3.5};
         memcpy(dp, v, sizeof v);
     } break;
     }
@@ -215,9 +219,13 @@ int sre_default_task(int kind, sre_task *t) {
     case SRE_BOB:
         q[0] = 1e5; q[1] = 1e3; q[2] = 1e3; q[3] = 1e2; r[0] = 1.0; t->rew_kind = SRE_REW_SCALED_EXP;
         break;
-    default:
+    case SRE_OMO:
         q[0] = 1e1; q[1] = 1e-2; r[0] = 1e-6; t->rew_kind = SRE_REW_QUADR;
         t->final_flags = SRE_FR_ENABLED | SRE_FR_ALWAYS_NEG; t->final_factor = 1e3;
+        break;
+    default:  // pendulum.py:82-88 -- idcs=[1] modulates theta_dot, as the reference does
+        t->state_des[0] = SRE_PI; q[0] = 1e-0; q[1] = 1e-3; r[0] = 1e-2;
+        t->rew_kind = SRE_REW_EXP; t->radial_mask = 1u << 1;
         break;
     }
     for (int i = 0; i < ds; i++) t->Q[i * ds + i] = q[i];
@@ -396,7 +404,8 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
         case SRE_QCP: r = rollout_f64_1(kc, kd, kp, k, s); break;
         case SRE_QBB: r = rollout_f64_2(kc, kd, kp, k, s); break;
         case SRE_BOB: r = rollout_f64_3(kc, kd, kp, k, s); break;
-        default: r = rollout_f64_4(kc, kd, kp, k, s); break;
+        case SRE_OMO: r = rollout_f64_4(kc, kd, kp, k, s); break;
+        default: r = rollout_f64_5(kc, kd, kp, k, s); break;
         }
     } else {
         KCfg<float> kc;
@@ -406,7 +415,8 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
         case SRE_QCP: r = rollout_f32_1(kc, kd, kp, k, s); break;
         case SRE_QBB: r = rollout_f32_2(kc, kd, kp, k, s); break;
         case SRE_BOB: r = rollout_f32_3(kc, kd, kp, k, s); break;
-        default: r = rollout_f32_4(kc, kd, kp, k, s); break;
+        case SRE_OMO: r = rollout_f32_4(kc, kd, kp, k, s); break;
+        default: r = rollout_f32_5(kc, kd, kp, k, s); break;
         }
     }
     if (r == 0) g_launch_count = 1;

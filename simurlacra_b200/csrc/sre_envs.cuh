@@ -459,4 +459,42 @@ template <typename R> struct Env<SRE_OMO, R> {
     }
 };
 
+// ======================================================================================================
+// PendulumSim -- pendulum.py:43-140 (under-actuated pendulum modelled as a rod)
+// state [th, thd]; obs [sin th, cos th, thd]; act [torque]; params (:96-104): gravity_const, pole_mass, pole_length,
+// pole_damping, torque_thold.  The init space is a SingularStateSpace (:75): the host passes it as a box with lo == up.
+// ======================================================================================================
+template <typename R> struct Env<SRE_PEND, R> {
+    static constexpr int DS = 2, DO = 3, DA = 1, DP = 5, NH = 0, DINIT = 2;
+    struct Consts {
+        R mgl2, d, inv_J;  // m g l / 2, damping, 1 / (m l^2 / 3)
+    };
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+        const double g = dp[0], m = dp[1], l = dp[2];
+        c.mgl2 = (R)(m * g * l / 2.0);
+        c.d = dp[3];
+        c.inv_J = (R)(1.0 / (m * (l * l) / 3.0));
+        st_lo[0] = (R)(-4 * SRE_PI); st_up[0] = (R)(4 * SRE_PI);  // :66-74
+        st_lo[1] = (R)(-4 * SRE_PI); st_up[1] = (R)(4 * SRE_PI);
+        act_lo[0] = -dp[4]; act_up[0] = dp[4];
+    }
+    // _step_dynamics :106-122: th_ddot = (tau - m g l / 2 sin th - d thd) / (m l^2 / 3); symplectic Euler
+    SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
+        const R thdd = (act[0] - c.mgl2 * trig[0] - c.d * s[1]) * c.inv_J;
+        s[1] += thdd * dt;
+        s[0] += s[1] * dt;
+    }
+    SRE_DEV static void observe(const R *s, R *obs, R *trig) {  // :93-94
+        m_sincos(s[0], obs[0], obs[1]);
+        obs[2] = s[1];
+        trig[0] = obs[0];
+        trig[1] = obs[1];
+    }
+    SRE_DEV static void reset_hidden(const R *dp, int flags, const R *s, R *h) {}
+    SRE_DEV static void state_from_init(const R *init, int n_cols, R *s) { s[0] = init[0]; s[1] = init[1]; }
+    SRE_DEV static void init_box(const R *dp, int wild_init, bool right, double *lo, double *up) {  // init_state = zeros
+        lo[0] = up[0] = 0.0; lo[1] = up[1] = 0.0;
+    }
+};
+
 }  // namespace sre

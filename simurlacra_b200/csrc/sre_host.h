@@ -31,12 +31,12 @@ extern thread_local int g_launch_count;
         }                                                                                \
     } while (0)
 
-static const int k_ds[SRE_N_KINDS] = {4, 4, 8, 4, 2};
-static const int k_do[SRE_N_KINDS] = {6, 5, 8, 4, 2};
-static const int k_da[SRE_N_KINDS] = {1, 1, 2, 1, 1};
-static const int k_dp[SRE_N_KINDS] = {11, 17, 20, 8, 3};
-static const int k_nh[SRE_N_KINDS] = {0, 1, 2, 0, 0};
-static const int k_dinit[SRE_N_KINDS] = {4, 4, 4, 4, 2};
+static const int k_ds[SRE_N_KINDS] = {4, 4, 8, 4, 2, 2};
+static const int k_do[SRE_N_KINDS] = {6, 5, 8, 4, 2, 3};
+static const int k_da[SRE_N_KINDS] = {1, 1, 2, 1, 1, 1};
+static const int k_dp[SRE_N_KINDS] = {11, 17, 20, 8, 3, 5};
+static const int k_nh[SRE_N_KINDS] = {0, 1, 2, 0, 0, 0};
+static const int k_dinit[SRE_N_KINDS] = {4, 4, 4, 4, 2, 2};
 
 template <typename R> inline void make_kcfg(const sre_env_cfg &c, KCfg<R> &k) {
     memset(&k, 0, sizeof(k));
@@ -102,5 +102,6 @@ SRE_DECL_ROLLOUT(1)
 SRE_DECL_ROLLOUT(2)
 SRE_DECL_ROLLOUT(3)
 SRE_DECL_ROLLOUT(4)
+SRE_DECL_ROLLOUT(5)
 
 }  // namespace sre

@@ -52,6 +52,7 @@ int policy_forward_tc_dispatch(const KPolicy &kp, const float *obs, int n_obs, f
     SRE_PF_CASE(8, 2)
     SRE_PF_CASE(4, 1)
     SRE_PF_CASE(2, 1)
+    SRE_PF_CASE(3, 1)
 #undef SRE_PF_CASE
     return -1000;
 }

@@ -251,7 +251,8 @@ __global__ void policy_forward_kernel(const __grid_constant__ KPolicy pol, const
     case SRE_QCP: { constexpr int K = SRE_QCP; BODY } break;              \
     case SRE_QBB: { constexpr int K = SRE_QBB; BODY } break;              \
     case SRE_BOB: { constexpr int K = SRE_BOB; BODY } break;              \
-    default: { constexpr int K = SRE_OMO; BODY } break;                   \
+    case SRE_OMO: { constexpr int K = SRE_OMO; BODY } break;              \
+    default: { constexpr int K = SRE_PEND; BODY } break;                  \
     }
 
 

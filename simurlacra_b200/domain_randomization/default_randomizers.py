@@ -96,6 +96,15 @@ def create_default_randomizer_omo() -> DomainRandomizer:  # :191-204
     return _from_rows(nom, [(k, "N", 3, 1e-3, _INF) for k in ("mass", "stiffness", "damping")])
 
 
+@default_randomizer(_PYSIM + "pendulum", "PendulumSim")
+def create_default_randomizer_pend() -> DomainRandomizer:  # :208-230
+    from ..environments.pysim.pendulum import PendulumSim
+
+    nom = PendulumSim.get_nominal_domain_param()
+    return _from_rows(nom, [(k, "N", 10, 1e-3, _INF) for k in ("gravity_const", "pole_mass", "pole_length", "pole_damping",
+                                                              "torque_thold")])
+
+
 @default_randomizer(_PYSIM + "quanser_ball_balancer", "QBallBalancerSim")
 def create_default_randomizer_qbb() -> DomainRandomizer:  # :233-307
     from ..environments.pysim.quanser_ball_balancer import QBallBalancerSim

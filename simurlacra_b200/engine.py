@@ -11,7 +11,7 @@ import torch
 
 from . import _lib as L
 
-KIND_BY_NAME = {"qq-su": L.QQ, "qcp-su": L.QCP, "qbb": L.QBB, "bob": L.BOB, "omo": L.OMO}
+KIND_BY_NAME = {"qq-su": L.QQ, "qcp-su": L.QCP, "qbb": L.QBB, "bob": L.BOB, "omo": L.OMO, "pend": L.PEND}
 
 
 def _ptr(t: Optional[torch.Tensor]):

@@ -20,6 +20,7 @@ from ... import _lib as L
 from ... import engine as E
 from ...spaces.base import Space
 from ...spaces.box import BoxSpace
+from ...spaces.singular import SingularStateSpace
 from ...tasks.base import Task
 from ..sim_base import SimEnv
 
@@ -200,7 +201,7 @@ class SimPyEnv(SimEnv):
         task = L.Task()
         self._task.fill(task)
         init_box = None
-        if (self._custom_init_space or self._pass_init_box) and type(self._init_space) is BoxSpace:
+        if (self._custom_init_space or self._pass_init_box) and type(self._init_space) in (BoxSpace, SingularStateSpace):
             init_box = self._init_space.bounds
         f = fusion or Fusion()
         return E.make_cfg(self.kind, self._dt, self._max_steps, dtype=self._dtype,

@@ -42,6 +42,7 @@ ENV_FILES = [
     ("traj_qbb_simple", "qbb", dict(simple_dynamics=True)),
     ("traj_bob", "bob", {}),
     ("traj_omo", "omo", {}),
+    ("traj_pend", "pend", {}),
     # stabilisation variants (same dynamics, other init / state spaces and tasks)
     ("traj_qq-st", "qq-su", dict(stab="qq-st")),
     ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st")),

@@ -16,6 +16,7 @@ from simurlacra_b200.environment_wrappers import (ActNormWrapper, DomainRandWrap
                                                    EnvWrapperObs, GaussianObsNoiseWrapper, ObsActCatWrapper)
 from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamSim
 from simurlacra_b200.environments.pysim.one_mass_oscillator import OneMassOscillatorSim
+from simurlacra_b200.environments.pysim.pendulum import PendulumSim
 from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
 from simurlacra_b200.environments.pysim.quanser_cartpole import QCartPoleStabSim, QCartPoleSwingUpSim
 from simurlacra_b200.environments.pysim.quanser_qube import QQubeStabSim, QQubeSwingUpSim
@@ -27,6 +28,8 @@ pytestmark = pytest.mark.gpu
 
 
 def _make_env(kind_name, dt, max_steps, kw, **extra):
+    if kind_name == "pend":
+        return PendulumSim(dt=dt, max_steps=max_steps, **extra)
     if kw.get("stab") == "qq-st":
         return QQubeStabSim(dt=dt, max_steps=max_steps, **extra)
     if kw.get("stab") == "qcp-st":

@@ -121,7 +121,7 @@ def test_trajectory_fp64_matches_reference(E, fname, kind_name, kw):
 # injected actions of the golden cases, so they are checked over the first 100 steps only
 FP32_TOL = {"traj_omo": (1e-4, None), "traj_bob": (1e-4, None), "traj_qbb": (1e-4, None), "traj_qbb_simple": (1e-4, None),
             "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100),
-            "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50)}
+            "traj_pend": (1e-4, None), "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50)}
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", ENV_FILES)

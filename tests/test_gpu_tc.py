@@ -37,7 +37,7 @@ def _torch_ref(w, sizes, obs):
     return x.numpy()
 
 
-@pytest.mark.parametrize("n_obs,n_act", [(6, 1), (5, 1), (8, 2), (4, 1), (2, 1)])
+@pytest.mark.parametrize("n_obs,n_act", [(6, 1), (5, 1), (8, 2), (4, 1), (2, 1), (3, 1)])
 @pytest.mark.parametrize("n", [1, 127, 128, 1000, 70001])
 def test_policy_forward_tensor_core_matches_fp32(E, n_obs, n_act, n):
     from simurlacra_b200 import _lib as L
@@ -74,7 +74,7 @@ def _qq_distr(E):
                                     clip_lo=clip.get(k, 1e-4)) for i, k in enumerate(names)])
 
 
-@pytest.mark.parametrize("kind_name,n_obs,n_act", [("qq-su", 6, 1), ("qbb", 8, 2), ("qcp-su", 5, 1)])
+@pytest.mark.parametrize("kind_name,n_obs,n_act", [("qq-su", 6, 1), ("qbb", 8, 2), ("qcp-su", 5, 1), ("pend", 3, 1)])
 @pytest.mark.parametrize("n_envs", [1, 130, 1000])
 def test_rollout_tensor_core_tracks_fp32_rollout(E, kind_name, n_obs, n_act, n_envs):
     """Same seeds, same weights: the tensor-core rollout follows the fp32-FMA rollout (identical DR draws and initial

@@ -380,3 +380,23 @@ def test_obs_norm_and_act_noise_wrappers_host_side():
     assert compile_chain(GaussianObsNoiseWrapper(ObsNormWrapper(QQubeSwingUpSim(dt=0.01)), noise_std=np.ones(6))) is None
     assert compile_chain(GaussianActNoiseWrapper(GaussianActNoiseWrapper(QQubeSwingUpSim(dt=0.01), noise_std=[0.2]),
                                                  noise_std=[0.2])) is None
+
+
+def test_pendulum_env_host_side():
+    """PendulumSim (pendulum.py:43-140): constructor checks, parameter-dependent action space, singular init space,
+    default randomizer, C-ABI configuration."""
+    from simurlacra_b200.environments.pysim.pendulum import PendulumSim
+
+    env = PendulumSim(dt=0.02, max_steps=100, init_state=np.array([0.3, -0.2]))
+    assert env.name == "pend" and env.obs_space.flat_dim == 3 and env.state_space.flat_dim == 2
+    assert env.act_space.bound_up[0] == 3.5
+    np.testing.assert_array_equal(env.init_space.sample_uniform(), [0.3, -0.2])
+    env.domain_param = dict(torque_thold=2.0)
+    assert env.act_space.bound_up[0] == 2.0 and env.domain_param["pole_mass"] == 1.0
+    with pytest.raises(pyrado.ShapeErr):
+        PendulumSim(dt=0.02, init_state=np.zeros(3))
+    rz = create_default_randomizer(env)
+    assert [p.name for p in rz.domain_params] == list(PendulumSim._param_names)
+    cfg = env._make_cfg()
+    assert cfg.kind == L.PEND and cfg.has_init_box == 1 and cfg.init_box_lo[0] == 0.3 and cfg.init_box_up[1] == -0.2
+    assert cfg.task.rew_kind == L.REW_EXP and cfg.task.radial_mask == 0b10 and cfg.task.state_des[0] == np.pi
