@@ -210,6 +210,12 @@ typedef struct sre_policy {
     int32_t reserved;
     float act_noise_scale[SRE_MAX_DA];
     float act_noise_mean[SRE_MAX_DA];
+    /* Parameter-exploration sampling (ParameterExplorationSampler, sampling/parameter_exploration_sampler.py:151-345:
+     * many policy-parameter sets x the same domains / init states): if group_size > 0, `weights` holds n_groups
+     * consecutive sets of n_weights floats and lane n of a sre_rollout launch evaluates set n / group_size.  Such
+     * policies read their set from global memory (no per-CTA staging, no tensor-core path). */
+    int64_t group_size;
+    int64_t n_groups;
 } sre_policy;
 
 /* Inputs / outputs of one rollout launch.  Replaces rollout() (sampling/rollout.py:63) run for N envs by

@@ -61,6 +61,7 @@ class Policy(C.Structure):
         ("act_noise", C.c_int),
         ("act_noise_scale", C.c_float * 2),
         ("act_noise_mean", C.c_float * 2),
+        ("group_size", C.c_long), ("n_weights", C.c_long),
     ]
 
 
@@ -191,8 +192,11 @@ def make_distr_table(entries):
 
 
 def make_policy(kind, weights=None, sizes=(), feats=(), hidden_nonlin=0, output_nonlin=0, cartpole_feats=False,
-                act_noise=0, act_noise_scale=(), act_noise_mean=()):
+                act_noise=0, act_noise_scale=(), act_noise_mean=(), group_size=0):
     p = Policy()
+    p.group_size = int(group_size)
+    if group_size and weights is not None:
+        p.n_weights = np.asarray(weights).reshape(-1).size // (np.asarray(weights).shape[0] if np.asarray(weights).ndim == 2 else 1)
     p.act_noise = int(act_noise)
     for i, v in enumerate(act_noise_scale):
         p.act_noise_scale[i] = v

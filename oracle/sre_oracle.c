@@ -889,6 +889,9 @@ typedef struct {
     int act_noise;
     float act_noise_scale[2];
     float act_noise_mean[2];
+    /* parameter exploration (sampling/parameter_exploration_sampler.py:267-345): lane n evaluates parameter set
+     * n / group_size of the n_weights-float sets stored back to back in `weights` (0: one set for all) */
+    long group_size, n_weights;
 } orc_policy;
 
 static float nonlin_f(int kind, float x) {
@@ -1054,7 +1057,13 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
             } else {
                 float of[ORC_MAX_DO], af[ORC_MAX_DA];
                 for (int i = 0; i < dob; i++) of[i] = (float)obs[i];
-                orc_policy_forward(pol, of, dob, af, da);
+                if (pol->group_size > 0) {
+                    orc_policy set = *pol;
+                    set.weights = pol->weights + (n / pol->group_size) * pol->n_weights;
+                    orc_policy_forward(&set, of, dob, af, da);
+                } else {
+                    orc_policy_forward(pol, of, dob, af, da);
+                }
                 if (pol->act_noise) {
                     /* act = dist(policy(obs) + mean).rsample(), float32 with torch's roundings; one Philox block per
                      * step (engine RNG specification): normal pair from words 0,1 with the exactly representable

@@ -104,6 +104,8 @@ class Policy(C.Structure):
         ("reserved", C.c_int32),
         ("act_noise_scale", C.c_float * MAX_DA),
         ("act_noise_mean", C.c_float * MAX_DA),
+        ("group_size", C.c_int64),
+        ("n_groups", C.c_int64),
     ]
 
 

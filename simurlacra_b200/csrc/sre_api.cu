@@ -98,6 +98,9 @@ int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp) {
     }
     SRE_CHECK_ARG(pol->n_weights == need, SRE_E_POLICY, "policy has %lld weights, layout needs %lld",
                   (long long)pol->n_weights, need);
+    SRE_CHECK_ARG(pol->group_size >= 0 && (pol->group_size == 0 || pol->n_groups >= 1), SRE_E_POLICY,
+                  "group_size %lld / n_groups %lld invalid", (long long)pol->group_size, (long long)pol->n_groups);
+    kp.group_size = pol->group_size;
     kp.n_layers = pol->n_layers;
     kp.n_feats = pol->n_feats;
     kp.hidden_nonlin = pol->hidden_nonlin;
@@ -379,6 +382,10 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
     if (e) return e;
     SRE_CHECK_ARG(!kp.cartpole_feats, SRE_E_UNSUPPORTED,
                   "cartpole_feats (the fork's 4-dim FNNPolicy input) is only available in sre_policy_forward");
+    if (kp.group_size > 0)
+        SRE_CHECK_ARG((io->n_envs + kp.group_size - 1) / kp.group_size <= pol->n_groups, SRE_E_POLICY,
+                      "%lld lanes in groups of %lld need more than the %lld parameter sets given", (long long)io->n_envs,
+                      (long long)kp.group_size, (long long)pol->n_groups);
     KDistr kd;
     e = make_kdistr(cfg, io->distr, io->n_distr, kd);
     if (e) return e;

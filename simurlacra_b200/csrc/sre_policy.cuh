@@ -18,6 +18,7 @@ struct KPolicy {
     const float *weights;  // device, torch layout
     long long n_weights;
     int smem_floats;  // size of the staged (re-laid-out) copy
+    long long group_size;  // > 0: lane n uses weights + (n / group_size) * n_weights (parameter exploration)
     int act_noise;    // SRE_ACT_NOISE_*
     float noise_scale[SRE_MAX_DA], noise_mean[SRE_MAX_DA];
 };

@@ -122,7 +122,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) +
                               (io.traj ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0), pol.weights);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
     else if (PV >= 16) Fast::stage(pol.weights, sm_w);
-    else if (PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) stage_generic(pol, sm_w);
+    else if ((PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) && pol.group_size == 0) stage_generic(pol, sm_w);
     __syncthreads();
 
     const long long N = io.n_envs;
@@ -313,8 +313,12 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 }
                 Tc::forward(tc, of, af);
             } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
-            else if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, sm_w, of, DO, af, DA);
-            else linear_forward<DO, DA>(pol, sm_w, of, af);
+            else {
+                // parameter exploration: this lane's own parameter set, straight from global memory (L2-resident)
+                const float *wsrc = pol.group_size > 0 ? pol.weights + (valid ? n / pol.group_size : 0) * pol.n_weights : sm_w;
+                if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, wsrc, of, DO, af, DA);
+                else linear_forward<DO, DA>(pol, wsrc, of, af);
+            }
             if (pol.act_noise && stepping)
                 add_act_noise<DA>(pol.act_noise, pol.noise_scale, pol.noise_mean, io.seed, genv, episode, (uint32_t)t_ep, af);
 #pragma unroll
@@ -456,13 +460,17 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
         return launch_rollout_pv<KIND, R, SRE_PV_ACTIONS>(cfg, distr, pol, io, stream);
     }
     if (pol.kind == SRE_POL_LINEAR) {
-        pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);
+        pol.smem_floats = pol.group_size > 0 ? 4 : (int)((pol.n_weights + 3) / 4 * 4);
         return launch_rollout_pv<KIND, R, SRE_PV_LINEAR>(cfg, distr, pol, io, stream);
     }
     // FNN: the register-resident fast path needs [do, H, H, da] with tanh hidden and linear output
     const bool two_hidden = pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
+    if (pol.group_size > 0) {  // per-lane parameter sets: only the un-staged forward passes apply
+        pol.smem_floats = 4;
+        return launch_rollout_pv<KIND, R, SRE_PV_GENERIC>(cfg, distr, pol, io, stream);
+    }
     if (two_hidden && pol.sizes[1] == 64 && pol.precision != SRE_PREC_FP32 && sizeof(R) == 4) {
         pol.smem_floats = 0;
         return pol.precision == SRE_PREC_TF32 ? launch_rollout_pv<KIND, R, SRE_PV_TC1>(cfg, distr, pol, io, stream)

@@ -148,7 +148,9 @@ def make_distr_table(entries: Sequence[dict]):
 
 def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), feats=(), hidden_nonlin: int = 0,
                 output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = 0, act_noise: int = 0,
-                act_noise_scale=(), act_noise_mean=()) -> L.Policy:
+                act_noise_scale=(), act_noise_mean=(), group_size: int = 0) -> L.Policy:
+    """`group_size` > 0: `weights` is a [n_sets, n_weights] matrix of parameter sets and lane n of a rollout launch
+    evaluates set n // group_size (parameter-exploration sampling)."""
     p = L.Policy()
     set_act_noise(p, act_noise, act_noise_scale, act_noise_mean)
     p.kind = kind
@@ -166,6 +168,10 @@ def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), fea
         p._keep = weights
         p.weights = weights.data_ptr()
         p.n_weights = weights.numel()
+        if group_size:
+            if weights.dim() != 2:
+                raise ValueError("grouped policies take a [n_sets, n_weights] weight matrix")
+            p.group_size, p.n_groups, p.n_weights = int(group_size), weights.shape[0], weights.shape[1]
     return p
 
 

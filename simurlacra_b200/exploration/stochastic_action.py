@@ -71,8 +71,8 @@ class StochasticActionExplStrat(Policy, ABC):
         if pol is not None:
             pol.engine_precision = value
 
-    def engine_desc(self, device):
-        desc = self.policy.engine_desc(device)
+    def engine_desc(self, device, param_sets=None, group_size: int = 0):
+        desc = self.policy.engine_desc(device, param_sets, group_size)
         if desc is None:
             return None
         kind, scale, mean = self.noise.engine_noise()

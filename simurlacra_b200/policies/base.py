@@ -103,9 +103,11 @@ class Policy(nn.Module, ABC):
         return res
 
     # ------------------------------------------------------------------ engine side
-    def engine_desc(self, device) -> Optional[L.Policy]:
+    def engine_desc(self, device, param_sets=None, group_size: int = 0) -> Optional[L.Policy]:
         """This policy as a C-ABI ``sre_policy`` (weights copied to `device` as one float32 vector), or None if the
-        kernels do not implement it; samplers then evaluate the module between step-kernel launches."""
+        kernels do not implement it; samplers then evaluate the module between step-kernel launches.
+        With `param_sets` (float32 CUDA [n_sets, num_param]) and `group_size`, lane n of a rollout launch evaluates
+        parameter set n // group_size instead of the module's own parameters (parameter-exploration sampling)."""
         return None
 
     def _engine_weights(self, device) -> torch.Tensor:

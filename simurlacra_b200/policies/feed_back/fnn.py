@@ -129,10 +129,11 @@ class FNNPolicy(Policy):
             obs = torch.cat([obs[..., 0:1], torch.sin(obs[..., 1:2]), torch.cos(obs[..., 1:2]), obs[..., 2:]], dim=-1)
         return self.net(obs)
 
-    def engine_desc(self, device):
+    def engine_desc(self, device, param_sets=None, group_size: int = 0):
         codes = self.net.engine_codes()
         if codes is None:
             return None
-        return E.make_policy(L.POL_FNN, self._engine_weights(device), sizes=self.net.sizes, hidden_nonlin=codes[0],
+        weights = self._engine_weights(device) if param_sets is None else param_sets
+        return E.make_policy(L.POL_FNN, weights, sizes=self.net.sizes, hidden_nonlin=codes[0],
                              output_nonlin=codes[1], cartpole_feats=self.cartpole_feats,
-                             precision=self.engine_precision)
+                             precision=self.engine_precision, group_size=group_size)

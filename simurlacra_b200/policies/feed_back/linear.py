@@ -48,8 +48,9 @@ class LinearPolicy(Policy):
         act = self.net(self.eval_feats(obs))
         return act if batched else act.flatten()
 
-    def engine_desc(self, device):
+    def engine_desc(self, device, param_sets=None, group_size: int = 0):
         codes = self._feats.engine_codes()
         if codes is None or len(codes) > L.MAX_FEATS:
             return None
-        return E.make_policy(L.POL_LINEAR, self._engine_weights(device), feats=codes)
+        weights = self._engine_weights(device) if param_sets is None else param_sets
+        return E.make_policy(L.POL_LINEAR, weights, feats=codes, group_size=group_size)

@@ -400,3 +400,43 @@ def test_pendulum_env_host_side():
     cfg = env._make_cfg()
     assert cfg.kind == L.PEND and cfg.has_init_box == 1 and cfg.init_box_lo[0] == 0.3 and cfg.init_box_up[1] == -0.2
     assert cfg.task.rew_kind == L.REW_EXP and cfg.task.radial_mask == 0b10 and cfg.task.state_des[0] == np.pi
+
+
+def test_parameter_exploration_sampler_host_side():
+    """ParameterExplorationSampler (parameter_exploration_sampler.py:151-216): constructor checks, the DR wrapper is
+    taken off the chain and kept as the source of domains, the result containers, and the grouped policy descriptor."""
+    from simurlacra_b200.policies import FNNPolicy
+    from simurlacra_b200.sampling import ParameterExplorationSampler, ParameterSample, ParameterSamplingResult
+
+    sim = QQubeSwingUpSim(dt=1 / 250.0, max_steps=50)
+    env = DomainRandWrapperLive(ActNormWrapper(sim), create_default_randomizer(sim))
+    pol = FNNPolicy(env.spec, hidden_sizes=[8], hidden_nonlin=torch.tanh)
+    for bad in (dict(num_init_states_per_domain=1.0, num_domains=2), dict(num_init_states_per_domain=1, num_domains="2")):
+        with pytest.raises(pyrado.TypeErr):
+            ParameterExplorationSampler(env, pol, **bad)
+    for bad in (dict(num_init_states_per_domain=0, num_domains=2), dict(num_init_states_per_domain=1, num_domains=0)):
+        with pytest.raises(pyrado.ValueErr):
+            ParameterExplorationSampler(env, pol, **bad)
+    pes = ParameterExplorationSampler(env, pol, num_init_states_per_domain=2, num_domains=3, seed=0)
+    assert pes.num_rollouts_per_param == 6 and isinstance(pes.env, ActNormWrapper) and pes._dr_wrapper is env
+    with pytest.raises(pyrado.ShapeErr):
+        pes.sample(torch.zeros(4, pol.num_param + 1))
+    with pytest.raises(pyrado.TypeErr):
+        pes.sample(torch.zeros(4, pol.num_param), init_states=np.zeros((6, 4)))
+
+    class _Ro:
+        def __init__(self, r):
+            self.r = r
+
+        def undiscounted_return(self):
+            return self.r
+
+    res = ParameterSamplingResult([ParameterSample(params=torch.full((3,), float(i)), rollouts=[_Ro(i), _Ro(i + 1.0)])
+                                   for i in range(4)])
+    assert len(res) == 4 and res.num_rollouts == 8 and res.parameters.shape == (4, 3)
+    np.testing.assert_array_equal(res.mean_returns, [0.5, 1.5, 2.5, 3.5])
+    assert res[2].mean_undiscounted_return == 2.5 and res[2].num_rollouts == 2
+    assert isinstance(res[1:], ParameterSamplingResult) and len(res[1:]) == 3 and len(res.rollouts[0]) == 2
+    with pytest.raises(ValueError):  # grouped descriptors take a matrix of parameter sets
+        E_make = __import__("simurlacra_b200.engine", fromlist=["make_policy"]).make_policy
+        E_make(L.POL_FNN, torch.zeros(10), sizes=[2, 2, 1], group_size=3)

@@ -180,6 +180,23 @@ def test_rollout_batch_deterministic_and_split_invariant(orc):
     assert len(np.unique(full["ret"])) == 16  # rollouts within one batch differ
 
 
+def test_grouped_policy_weights(orc):
+    """Parameter-exploration layout (parameter_exploration_sampler.py:302-313: every parameter set runs the same
+    rollouts): lanes [p R, (p+1) R) of a grouped batch == a batch of R lanes at env_offset p R with set p alone."""
+    R, P, H = 3, 4, 40
+    sizes = [6, 8, 1]
+    rng = np.random.RandomState(0)
+    w = (rng.randn(P, 6 * 8 + 8 + 8 + 1) * 0.4).astype(np.float32)
+    g = orc.rollout_batch(orc.QQ, 1 / 250.0, H, P * R, H, policy=orc.make_policy(orc.POL_FNN, w, sizes=sizes, group_size=R),
+                          act_norm=True, seed=5)
+    for p in range(P):
+        s = orc.rollout_batch(orc.QQ, 1 / 250.0, H, R, H, policy=orc.make_policy(orc.POL_FNN, w[p], sizes=sizes),
+                              act_norm=True, seed=5, env_offset=p * R)
+        np.testing.assert_array_equal(g["state"][:, p * R:(p + 1) * R], s["state"])
+        np.testing.assert_array_equal(g["ret"][p * R:(p + 1) * R], s["ret"])
+    assert len(np.unique(g["act"][0, ::R, 0])) == P
+
+
 def test_returns_match_reference(orc):
     """orc_returns against discounted_value / gae_returns of the unmodified reference (tests/golden/returns_reference.npz,
     generated by oracle/gen_golden.py): single complete rollouts, then all of them chained in one lane (auto-reset
