@@ -372,9 +372,55 @@ def gen_stab_envs():
     gen_env_trajs("qcp-st", n_cases=4, simple_dynamics=True)
 
 
+def gen_wrappers():
+    """SURVEY.md 8(f) rank 2, the stateful / shape-changing step-path wrappers: ActDelayWrapper, DownsamplingWrapper,
+    ObsPartialWrapper, ObsVelFiltWrapper, StateAugmentationWrapper of the unmodified reference around
+    QQubeSwingUpSim(dt=1/250) with injected actions; observations as the wrapper returns them (reset + every step)."""
+    from pyrado.environment_wrappers.action_delay import ActDelayWrapper
+    from pyrado.environment_wrappers.downsampling import DownsamplingWrapper
+    from pyrado.environment_wrappers.observation_partial import ObsPartialWrapper
+    from pyrado.environment_wrappers.observation_velfilter import ObsVelFiltWrapper
+    from pyrado.environment_wrappers.state_augmentation import StateAugmentationWrapper
+
+    rng = np.random.RandomState(77)
+    H = 60
+    act = rng.uniform(-3.0, 3.0, size=(H, 1))
+    s0 = np.array([0.1, -0.2, 0.3, -0.4])
+    dp = dict(mass_pend_pole=0.03, length_pend_pole=0.15)
+    cases = dict(
+        delay3=lambda e: ActDelayWrapper(e, delay=3),
+        delay3_norm=lambda e: ActNormWrapper(ActDelayWrapper(e, delay=3)),
+        down4=lambda e: DownsamplingWrapper(e, factor=4),
+        partial_mask=lambda e: ObsPartialWrapper(e, mask=[0, 0, 0, 0, 1, 1]),
+        partial_keep=lambda e: ObsPartialWrapper(e, idcs=["sin_theta", "cos_theta", "theta_dot"], keep_selected=True),
+        velfilt=lambda e: ObsVelFiltWrapper(e, idcs_pos=["theta", "alpha"], idcs_vel=["theta_dot", "alpha_dot"]),
+        augment=lambda e: StateAugmentationWrapper(e, domain_param=["mass_pend_pole", "length_pend_pole"]),
+        augment_fixed=lambda e: StateAugmentationWrapper(e, domain_param=["mass_pend_pole", "length_pend_pole"], fixed=True),
+    )
+    out = dict(act=act, init_state=s0, dp_keys=np.array(list(dp.keys())), dp_vals=np.array(list(dp.values())))
+    for name, mk in cases.items():
+        env = mk(QQubeSwingUpSim(dt=1 / 250.0, max_steps=H))
+        a = act / 5.0 if name.endswith("_norm") else act  # normalised units for the ActNorm chain
+        obs = [np.asarray(env.reset(init_state=s0.copy(), domain_param=dict(dp)), dtype=np.float64).copy()]
+        states, rews = [env.state.copy()], []
+        for t in range(H):
+            o, r, d, _ = env.step(a[t].copy())
+            obs.append(np.asarray(o, dtype=np.float64).copy())
+            states.append(env.state.copy())
+            rews.append(float(r))
+            if d:
+                break
+        out[name + "_len"] = np.array(len(rews))
+        out[name + "_obs"], out[name + "_states"], out[name + "_rews"] = np.array(obs), np.array(states), np.array(rews)
+        out[name + "_obs_lo"], out[name + "_obs_up"] = env.obs_space.bound_lo, env.obs_space.bound_up
+    np.savez_compressed(osp.join(OUT, "wrappers_reference.npz"), **out)
+    print("wrappers_reference.npz", {k: v.shape for k, v in out.items() if k.endswith("_obs")})
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
-        {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6)}[sys.argv[1]]()
+        {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6),
+         "wrappers": gen_wrappers}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)

@@ -52,6 +52,27 @@ class Space(ABC):
     def copy(self):
         return deepcopy(self)
 
+    def create_mask(self, *idcs) -> np.ndarray:
+        """Boolean mask with True at the given indices; an index is a number or one of the space's labels
+        (spaces/base.py:103-136)."""
+        from ..utils.exceptions import TypeErr, ValueErr
+
+        mask = np.zeros(self.shape, dtype=bool)
+        if len(idcs) == 1 and not isinstance(idcs[0], str) and hasattr(idcs[0], "__iter__"):
+            idcs = idcs[0]
+        for idx in idcs:
+            if isinstance(idx, str):
+                if self.labels is None:
+                    raise TypeErr(msg="The space must be labeled to use label-based indexing!")
+                hits = np.argwhere(np.asarray(self.labels) == idx)
+                if len(hits) == 0:
+                    raise ValueErr(msg=f"Label {idx} not found in {self}")
+                idx = tuple(hits[0])
+            if np.all(mask[idx]):
+                raise ValueErr(msg=f"Duplicate index {idx}")
+            mask[idx] = True
+        return mask
+
     @abstractmethod
     def subspace(self, idcs: Union[np.ndarray, int, slice]):
         raise NotImplementedError

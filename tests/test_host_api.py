@@ -440,3 +440,59 @@ def test_parameter_exploration_sampler_host_side():
     with pytest.raises(ValueError):  # grouped descriptors take a matrix of parameter sets
         E_make = __import__("simurlacra_b200.engine", fromlist=["make_policy"]).make_policy
         E_make(L.POL_FNN, torch.zeros(10), sizes=[2, 2, 1], group_size=3)
+
+
+def test_stateful_step_wrappers_host_side():
+    """ActDelay / Downsampling / ObsPartial / ObsVelFilt / StateAugmentation (environment_wrappers/*.py): constructor
+    checks, reported spaces, wrapper-owned domain parameters, Space.create_mask (spaces/base.py:103-136)."""
+    from simurlacra_b200.environment_wrappers import (ActDelayWrapper, DownsamplingWrapper, ObsPartialWrapper,
+                                                       ObsVelFiltWrapper, StateAugmentationWrapper)
+
+    sim = QQubeSwingUpSim(dt=1 / 250.0, max_steps=50)
+    sp = sim.obs_space
+    np.testing.assert_array_equal(sp.create_mask("theta_dot", 0), [1, 0, 0, 0, 1, 0])
+    np.testing.assert_array_equal(sp.create_mask([1, "alpha_dot"]), [0, 1, 0, 0, 0, 1])
+    with pytest.raises(pyrado.ValueErr):
+        sp.create_mask("nope")
+    with pytest.raises(pyrado.ValueErr):
+        sp.create_mask(1, 1)
+    part = ObsPartialWrapper(sim, idcs=["theta_dot", "alpha_dot"])
+    assert part.obs_space.flat_dim == 4 and list(part.obs_space.labels) == ["sin_theta", "cos_theta", "sin_alpha", "cos_alpha"]
+    assert ObsPartialWrapper(sim, mask=[1, 1, 0, 0, 0, 0], keep_selected=True).obs_space.flat_dim == 2
+    with pytest.raises(pyrado.ShapeErr):
+        ObsPartialWrapper(sim, mask=[1, 0])
+    np.testing.assert_array_equal(part._process_obs(np.arange(6.0)), [0, 1, 2, 3])
+    np.testing.assert_array_equal(part._process_obs(torch.arange(12.0).reshape(2, 6)), [[0, 1, 2, 3], [6, 7, 8, 9]])
+    dl = ActDelayWrapper(sim, delay=2)
+    assert dl.delay == 2 and dl.domain_param["act_delay"] == 2
+    with pytest.raises(pyrado.ValueErr):
+        dl.delay = -1
+    dl._act_queue = [None, None]
+    outs = [dl._process_act(np.array([float(i)])) for i in range(1, 5)]
+    np.testing.assert_array_equal(np.concatenate(outs), [0, 0, 1, 2])
+    ds = DownsamplingWrapper(sim, factor=3)
+    assert ds.domain_param["downsampling"] == 3
+    np.testing.assert_array_equal(np.concatenate([ds._process_act(np.array([float(i)])) for i in range(7)]), [0, 0, 0, 3, 3, 3, 6])
+    np.testing.assert_allclose([ds._process_obs(np.array([float(i)]))[0] for i in range(5)], [0, 0.5, 1, 2, 3])
+    ds.factor = 2
+    assert ds._cnt == 0
+    vf = ObsVelFiltWrapper(sim, idcs_pos=["theta", "alpha"], idcs_vel=["theta_dot", "alpha_dot"])
+    assert vf.b.dtype == np.float32 and vf.z.shape == (1, 2) and vf.obs_space == sim.obs_space
+    with pytest.raises(pyrado.ValueErr):
+        ObsVelFiltWrapper(sim, idcs_pos=["theta"])
+    with pytest.raises(pyrado.ShapeErr):
+        ObsVelFiltWrapper(sim, mask_pos=[1, 0], idcs_vel=["theta_dot"])
+    # constant position -> zero velocity once the filter starts in steady state; a ramp -> its slope
+    vf.init_filter(np.array([0.5, -0.5, 0.0, 0.0]))
+    np.testing.assert_allclose(vf._filter(np.array([0.5, -0.5])), 0.0, atol=1e-6)
+    from scipy import signal
+
+    vf.init_filter(np.zeros(4))
+    x = np.random.RandomState(0).randn(50, 2)
+    ys = np.array([vf._filter(xi) for xi in x])
+    np.testing.assert_allclose(ys, signal.lfilter(vf.b, vf.a, x, axis=0), rtol=1e-10, atol=1e-10)  # what the reference runs
+    aug = StateAugmentationWrapper(sim, domain_param=["mass_pend_pole", "gravity_const"])
+    assert aug.obs_space.flat_dim == 8 and list(aug.obs_space.labels[-2:]) == ["mass_pend_pole", "gravity_const"]
+    np.testing.assert_allclose(aug.obs_space.bound_up[-2:], 1.5 * aug.nominal)
+    assert aug.offset == 6 and aug.mask.sum() == 2
+    assert StateAugmentationWrapper(sim).obs_space.flat_dim == 6 + len(sim.domain_param)
