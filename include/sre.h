@@ -54,6 +54,7 @@ extern "C" {
 /* cfg.flags */
 #define SRE_F_SIMPLE_DYN 1 /* simple_dynamics=True (quanser_cartpole.py:515, quanser_ball_balancer.py:64) */
 #define SRE_F_QCP_STAB 2   /* QCartPoleStabSim state space: theta in pi +- 15 deg, |theta_dot| <= 2 pi (quanser_cartpole.py:473-482) */
+#define SRE_F_DISC_ACT 4   /* BallOnBeamDiscSim: actions are projected onto the 3-element DiscreteSpace linspace(lo, up, 3) (ball_on_beam.py:155-162, spaces/discrete.py:119-127) */
 
 /* reward kinds: tasks/reward_functions.py:176 (Quadr), :224 (ExpQuadr), :247 (ScaledExpQuadr) */
 #define SRE_REW_QUADR 0

@@ -29,7 +29,7 @@ warnings.filterwarnings("ignore")
 
 import torch  # noqa: E402
 import pyrado  # noqa: E402
-from pyrado.environments.pysim.ball_on_beam import BallOnBeamSim  # noqa: E402
+from pyrado.environments.pysim.ball_on_beam import BallOnBeamDiscSim, BallOnBeamSim  # noqa: E402
 from pyrado.environments.pysim.one_mass_oscillator import OneMassOscillatorSim  # noqa: E402
 from pyrado.environments.pysim.pendulum import PendulumSim  # noqa: E402
 from pyrado.environments.pysim.quanser_ball_balancer import QBallBalancerSim  # noqa: E402
@@ -69,6 +69,8 @@ def make_env(name, **kw):
                                 simple_dynamics=kw.get("simple_dynamics", False))
     if name == "bob":
         return BallOnBeamSim(dt=kw.get("dt", 0.01), max_steps=kw.get("max_steps", 500))
+    if name == "bob-d":
+        return BallOnBeamDiscSim(dt=kw.get("dt", 0.01), max_steps=kw.get("max_steps", 500))
     if name == "omo":
         return OneMassOscillatorSim(dt=kw.get("dt", 0.02), max_steps=kw.get("max_steps", 300),
                                     task_args=dict(state_des=np.array([0.5, 0.0])))
@@ -83,6 +85,7 @@ RANDOMIZERS = {
     "qcp-st": create_default_randomizer_qcp,
     "qbb": create_default_randomizer_qbb,
     "bob": create_default_randomizer_bob,
+    "bob-d": create_default_randomizer_bob,
     "omo": create_default_randomizer_omo,
 }
 
@@ -420,7 +423,7 @@ def gen_wrappers():
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
         {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6),
-         "wrappers": gen_wrappers}[sys.argv[1]]()
+         "wrappers": gen_wrappers, "bob-d": lambda: gen_env_trajs("bob-d", n_cases=6)}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)

@@ -18,6 +18,7 @@ QQ, QCP, QBB, BOB, OMO, PEND = 0, 1, 2, 3, 4, 5
 KIND_BY_NAME = {"qq-su": QQ, "qcp-su": QCP, "qbb": QBB, "bob": BOB, "omo": OMO, "pend": PEND}
 F_SIMPLE_DYN = 1
 F_QCP_STAB = 2
+F_DISC_ACT = 4
 REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2
 FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8, 16
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3
@@ -229,12 +230,13 @@ def policy_forward(pol, obs, n_act):
 class OracleEnv:
     """One environment of the C oracle with the reference's reset/step semantics (fp64)."""
 
-    def __init__(self, kind, dt, max_steps=0, simple_dynamics=False, long_pole=False, stab=False):
+    def __init__(self, kind, dt, max_steps=0, simple_dynamics=False, long_pole=False, stab=False, disc_act=False):
         self.kind = kind
         self.d = dims(kind)
         self._L = lib()
         self._h = self._L.orc_create(kind, float(dt), int(max_steps),
-                                     (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0), int(long_pole))
+                                     (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0)
+                                     | (F_DISC_ACT if disc_act else 0), int(long_pole))
 
     def __del__(self):
         if getattr(self, "_h", None):
@@ -333,12 +335,12 @@ class OracleEnv:
 def rollout_batch(kind, dt, max_steps, N, H, *, policy, simple_dynamics=False, long_pole=False, wild_init=0,
                   task=None, act_norm=False, noise_std=None, noise_mean=None, params=None, distr=None, init=None,
                   init_box=None, actions=None, seed=0, env_offset=0, episode=0, stop_on_done=True, record=True,
-                  n_threads=0, stab=False, obs_norm=None, env_act_noise=None):
+                  n_threads=0, stab=False, obs_norm=None, env_act_noise=None, disc_act=False):
     """Run N independent rollouts on the CPU oracle. Returns a dict of arrays ([T, N, d] layout) + 'steps'."""
     d = dims(kind)
     cfg = RolloutCfg()
     cfg.kind, cfg.long_pole, cfg.wild_init = kind, int(long_pole), wild_init
-    cfg.flags = (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0)
+    cfg.flags = (F_SIMPLE_DYN if simple_dynamics else 0) | (F_QCP_STAB if stab else 0) | (F_DISC_ACT if disc_act else 0)
     if obs_norm is not None:
         cfg.obs_norm = 1
         for i, v in enumerate(np.asarray(obs_norm[0], dtype=np.float64).reshape(-1)): cfg.obs_lb[i] = v

@@ -45,6 +45,7 @@
 /* flags */
 #define ORC_F_SIMPLE_DYN 1 /* QCartPole / QBB simple_dynamics=True */
 #define ORC_F_QCP_STAB 2   /* QCartPoleStabSim state space, quanser_cartpole.py:473-489 */
+#define ORC_F_DISC_ACT 4   /* BallOnBeamDiscSim: 3-element DiscreteSpace over the action bounds, ball_on_beam.py:155-162 */
 
 /* reward function kinds: tasks/reward_functions.py:176 (Quadr), :224 (ExpQuadr), :247 (ScaledExpQuadr) */
 #define ORC_REW_QUADR 0
@@ -648,6 +649,20 @@ static void pend_step(orc_env *e, double act) {
 
 /* Env.limit_act -> BoxSpace.project_to, environments/base.py:215-222, spaces/box.py:180-184 */
 void orc_limit_act(const orc_env *e, const double *act, double *out) {
+    if (e->flags & ORC_F_DISC_ACT) {
+        /* DiscreteSpace.project_to (spaces/discrete.py:119-127) over eles = linspace(lo, up, 3): an action that
+         * np.isclose()s an element (|ele - a| <= 1e-8 + 1e-5 |a|) passes unchanged, else the closest element (first
+         * one on ties, np.argmin) */
+        double lo = e->act_lo[0], up = e->act_up[0], a = act[0];
+        double eles[3] = {lo, lo + (up - lo) / 2.0, up};
+        int close = 0, best = 0;
+        for (int k = 0; k < 3; k++) {
+            if (fabs(eles[k] - a) <= 1e-8 + 1e-5 * fabs(a)) close = 1;
+            if (fabs(a - eles[k]) < fabs(a - eles[best])) best = k;
+        }
+        out[0] = close ? a : eles[best];
+        return;
+    }
     for (int i = 0; i < k_da[e->kind]; i++) out[i] = fmin(fmax(act[i], e->act_lo[i]), e->act_up[i]);
 }
 
@@ -1121,6 +1136,7 @@ long orc_rollout_batch(const orc_rollout_cfg *cfg, const orc_policy *pol, long N
                     double lo = cfg->act_norm ? -1.0 : e.act_lo[i], up = cfg->act_norm ? 1.0 : e.act_up[i];
                     out->act_app[(t * N + n) * da + i] = fmin(fmax(act[i], lo), up);
                 }
+                if ((e.flags & ORC_F_DISC_ACT) && !cfg->act_norm) orc_limit_act(&e, act, out->act_app + (t * N + n) * da);
             }
             int d = orc_step(&e, act_env, obs, &rew);
             done = (d != 0);

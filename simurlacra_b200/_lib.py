@@ -18,6 +18,7 @@ F32, F64 = 0, 1
 MAX_DS, MAX_DO, MAX_DA, MAX_DP, MAX_NH, MAX_DISTR, MAX_LAYERS, MAX_WIDTH, MAX_FEATS = 8, 8, 2, 20, 2, 32, 8, 128, 12
 F_SIMPLE_DYN = 1
 F_QCP_STAB = 2
+F_DISC_ACT = 4
 REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2
 FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8, 16
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3

@@ -179,14 +179,31 @@ template <int KIND, typename R> struct Lane {
         return -scale;
     }
 
+    // Env.limit_act (environments/base.py:215-222): BoxSpace.project_to clips (box.py:180); the DiscreteSpace of
+    // BallOnBeamDiscSim keeps an action that np.isclose()s one of its three elements and else takes the closest
+    // element, the first one on ties (discrete.py:119-127).
+    SRE_DEV void limit_act(const KCfg<R> &cfg, const R *act, R *a) const {
+        if (KIND == SRE_BOB && (cfg.flags & SRE_F_DISC_ACT)) {  // the flag exists for the ball-on-beam only
+            const R lo = act_lo[0], up = act_up[0], x = act[0], mid = lo + (up - lo) / (R)2;
+            const R d0 = m_abs(x - lo), d1 = m_abs(x - mid), d2 = m_abs(x - up);
+            const R tol = (R)1e-8 + (R)1e-5 * m_abs(x);
+            R e = lo, d = d0;
+            if (d1 < d) { e = mid; d = d1; }
+            if (d2 < d) e = up;
+            a[0] = (d0 <= tol || d1 <= tol || d2 <= tol) ? x : e;
+            return;
+        }
+#pragma unroll
+        for (int i = 0; i < E::DA; i++) a[i] = m_min(m_max(act[i], act_lo[i]), act_up[i]);
+    }
+
     // SimPyEnv.step (base.py:217-241).  act: inner-env units, unclipped.  Returns done; *inside gets the
     // contains() code (-1 = NaN state, the reference raises ValueErr at spaces/box.py:142).
     SRE_DEV bool step(const KCfg<R> &cfg, const R *act, R &rew, int &inside) {
         const long long remaining = cfg.max_steps > 0 ? cfg.max_steps - (curr_step + 1) : 0;
         R r = step_rew<E::DS, E::DA, R>(cfg.task, s, act, c_max);
         R a[E::DA];
-#pragma unroll
-        for (int i = 0; i < E::DA; i++) a[i] = m_min(m_max(act[i], act_lo[i]), act_up[i]);  // limit_act, box.py:180
+        limit_act(cfg, act, a);
         E::step(c, cfg.dt, cfg.flags, s, h, a, trig);  // trig belongs to the pre-step state
         curr_step += 1;
         inside = contains();

@@ -345,6 +345,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 rec[RC::OFF_ACT + i] = act[i];
                 rec[RC::OFF_ACT_APP + i] = m_min(m_max(act[i], lo), up);
             }
+            if (KIND == SRE_BOB && (cfg.flags & SRE_F_DISC_ACT) && !cfg.act_norm) L.limit_act(cfg, act, &rec[RC::OFF_ACT_APP]);
 #pragma unroll
             for (int i = 0; i < DO; i++) {
                 rec[RC::OFF_OBS + i] = obs[i];

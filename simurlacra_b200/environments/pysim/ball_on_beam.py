@@ -1,9 +1,10 @@
-"""BallOnBeamSim (pyrado/environments/pysim/ball_on_beam.py:41-136)."""
+"""BallOnBeamSim and BallOnBeamDiscSim (pyrado/environments/pysim/ball_on_beam.py:41-136, :139-162)."""
 import numpy as np
 
 from ... import _lib as L
 from ...spaces.box import BoxSpace
 from ...spaces.compound import CompoundSpace
+from ...spaces.discrete import DiscreteSpace
 from ...tasks.desired_state import DesStateTask
 from ...tasks.reward_functions import ScaledExpQuadrErrRewFcn
 from .base import SimPyEnv
@@ -41,3 +42,19 @@ class BallOnBeamSim(SimPyEnv):
         R = task_args.get("R", np.eye(self.spec.act_space.flat_dim))
         return DesStateTask(self.spec, state_des,
                             ScaledExpQuadrErrRewFcn(Q, R, self.state_space, self.act_space, min_rew=1e-4))
+
+
+class BallOnBeamDiscSim(BallOnBeamSim):
+    """Ball-on-beam simulation environment with discrete actions: every action is projected onto
+    {-max_act, 0, +max_act} (the kernels' `SRE_F_DISC_ACT`)."""
+
+    name: str = "bob-d"
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self._flags |= L.F_DISC_ACT
+
+    def _create_spaces(self):  # :153-162
+        super()._create_spaces()
+        min_act, max_act = self._act_space.bounds
+        self._act_space = DiscreteSpace(np.linspace(min_act, max_act, num=3, endpoint=True), labels=["tau"])

@@ -47,6 +47,7 @@ ENV_FILES = [
     ("traj_qq-st", "qq-su", dict(stab="qq-st")),
     ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st")),
     ("traj_qcp-st_simple", "qcp-su", dict(long_pole=True, simple_dynamics=True, stab="qcp-st")),
+    ("traj_bob-d", "bob", dict(disc_act=True)),  # BallOnBeamDiscSim: actions projected onto {-max, 0, +max}
 ]
 
 # task_args defaults of the stabilisation envs: quanser_qube.py:223-229 (ExpQuadrErrRewFcn), quanser_cartpole.py:491-500

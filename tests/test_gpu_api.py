@@ -14,7 +14,7 @@ from simurlacra_b200.domain_randomization import DomainRandomizer, NormalDomainP
 from simurlacra_b200.domain_randomization.default_randomizers import create_default_randomizer
 from simurlacra_b200.environment_wrappers import (ActNormWrapper, DomainRandWrapperBuffer, DomainRandWrapperLive,
                                                    EnvWrapperObs, GaussianObsNoiseWrapper, ObsActCatWrapper)
-from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamSim
+from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamDiscSim, BallOnBeamSim
 from simurlacra_b200.environments.pysim.one_mass_oscillator import OneMassOscillatorSim
 from simurlacra_b200.environments.pysim.pendulum import PendulumSim
 from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
@@ -42,6 +42,8 @@ def _make_env(kind_name, dt, max_steps, kw, **extra):
                                    simple_dynamics=kw.get("simple_dynamics", False), **extra)
     if kind_name == "qbb":
         return QBallBalancerSim(dt=dt, max_steps=max_steps, simple_dynamics=kw.get("simple_dynamics", False), **extra)
+    if kind_name == "bob" and kw.get("disc_act"):
+        return BallOnBeamDiscSim(dt=dt, max_steps=max_steps, **extra)
     if kind_name == "bob":
         return BallOnBeamSim(dt=dt, max_steps=max_steps, **extra)
     return OneMassOscillatorSim(dt=dt, max_steps=max_steps, task_args=OMO_TASK, **extra)

@@ -37,6 +37,8 @@ def _cfg(E, kind_name, dt, max_steps, kw, dtype, **extra):
                            rew_kind=L.REW_EXP if t["rew"] == "exp" else L.REW_QUADR, radial_idcs=[1],
                            final_flags=(L.FR_ENABLED | L.FR_STATE_DEP | L.FR_TIME_DEP) if t["final"] else 0)
         extra = dict(extra, flags=L.F_QCP_STAB if stab == "qcp-st" else 0)
+    if kw.get("disc_act"):
+        extra = dict(extra, flags=extra.get("flags", 0) | L.F_DISC_ACT)
     return E.make_cfg(kind, dt, max_steps, dtype=dtype, simple_dynamics=kw.get("simple_dynamics", False),
                       long_pole=kw.get("long_pole", False), task=task, **extra)
 
@@ -121,7 +123,8 @@ def test_trajectory_fp64_matches_reference(E, fname, kind_name, kw):
 # injected actions of the golden cases, so they are checked over the first 100 steps only
 FP32_TOL = {"traj_omo": (1e-4, None), "traj_bob": (1e-4, None), "traj_qbb": (1e-4, None), "traj_qbb_simple": (1e-4, None),
             "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100),
-            "traj_pend": (1e-4, None), "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50)}
+            "traj_pend": (1e-4, None), "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50),
+            "traj_bob-d": (1e-4, None)}
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", ENV_FILES)

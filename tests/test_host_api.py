@@ -496,3 +496,30 @@ def test_stateful_step_wrappers_host_side():
     np.testing.assert_allclose(aug.obs_space.bound_up[-2:], 1.5 * aug.nominal)
     assert aug.offset == 6 and aug.mask.sum() == 2
     assert StateAugmentationWrapper(sim).obs_space.flat_dim == 6 + len(sim.domain_param)
+
+
+def test_discrete_space_and_ball_on_beam_disc():
+    """DiscreteSpace (spaces/discrete.py:39-175) and BallOnBeamDiscSim (ball_on_beam.py:139-162)."""
+    from simurlacra_b200.environments.pysim.ball_on_beam import BallOnBeamDiscSim
+    from simurlacra_b200.spaces import DiscreteSpace
+
+    sp = DiscreteSpace(np.array([[-2.0], [0.0], [2.0]]), labels=["tau"])
+    assert sp.num_ele == 3 and sp.flat_dim == 1 and sp.shape == (1,) and sp.bound_abs_up[0] == 2.0
+    assert sp.contains(np.array([2.0])) and not sp.contains(np.array([1.0]))
+    np.testing.assert_array_equal(sp.project_to(np.array([0.9])), [0.0])
+    np.testing.assert_array_equal(sp.project_to(np.array([1.1])), [2.0])
+    np.testing.assert_array_equal(sp.project_to(np.array([-7.0])), [-2.0])
+    np.testing.assert_array_equal(sp.project_to(np.array([1.0])), [0.0])  # tie -> first of the closest (np.argmin)
+    assert sp.project_to(np.array([1e-9]))[0] == 1e-9  # np.isclose to an element: passes unchanged
+    with pytest.raises(pyrado.ShapeErr):
+        sp.contains(np.zeros(2))
+    with pytest.raises(pyrado.ValueErr):
+        sp.contains(np.array([np.nan]))
+    assert sp.sample_uniform()[0] in (-2.0, 0.0, 2.0)
+    assert DiscreteSpace.cat([sp, None, sp]).num_ele == 6 and DiscreteSpace([1, 2, 3]).eles.dtype == np.intc
+    env = BallOnBeamDiscSim(dt=0.01, max_steps=100)
+    assert env.name == "bob-d" and isinstance(env.act_space, DiscreteSpace)
+    np.testing.assert_allclose(env.act_space.eles.reshape(-1), [-29.43, 0.0, 29.43])
+    assert env._make_cfg().flags & L.F_DISC_ACT
+    env.domain_param = dict(beam_length=1.0)
+    np.testing.assert_allclose(env.act_space.eles.reshape(-1), [-14.715, 0.0, 14.715])
