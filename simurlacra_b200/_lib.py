@@ -9,7 +9,7 @@ import os
 import os.path as osp
 
 _HERE = osp.dirname(osp.abspath(__file__))
-LIB_PATH = osp.join(_HERE, "lib", "libsre_b200.so")
+LIB_PATH = os.environ.get("SRE_B200_LIB") or osp.join(_HERE, "lib", "libsre_b200.so")  # override: kernel experiments
 CSRC_DIR = osp.join(_HERE, "csrc")
 
 # ---- constants (include/sre.h) ----

@@ -83,7 +83,37 @@ SRE_DEV void umma_commit(uint32_t bar) {
 SRE_DEV void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
+// SRE_TC_WAIT: 0 = poll try_wait back to back, 1 = try_wait with a suspend-time hint of SRE_TC_WAIT_NS, 2 = sleep
+// SRE_TC_WAIT_NS between polls (a polling warp takes issue slots from the warps that have work)
+#ifndef SRE_TC_WAIT
+#define SRE_TC_WAIT 0
+#endif
+#ifndef SRE_TC_WAIT_NS
+#define SRE_TC_WAIT_NS 200
+#endif
 SRE_DEV void mbar_wait(uint32_t bar, uint32_t parity) {
+#if SRE_TC_WAIT == 1
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        ::"r"(bar), "r"(parity), "r"((uint32_t)SRE_TC_WAIT_NS)
+        : "memory");
+#elif SRE_TC_WAIT == 2
+    uint32_t ok;
+    for (;;) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) break;
+        __nanosleep(SRE_TC_WAIT_NS);
+    }
+#else
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
@@ -93,6 +123,7 @@ SRE_DEV void mbar_wait(uint32_t bar, uint32_t parity) {
         "DONE_%=:\n\t}"
         ::"r"(bar), "r"(parity)
         : "memory");
+#endif
 }
 SRE_DEV void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 SRE_DEV void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
