@@ -213,8 +213,10 @@ typedef struct sre_policy {
     float act_noise_mean[SRE_MAX_DA];
     /* Parameter-exploration sampling (ParameterExplorationSampler, sampling/parameter_exploration_sampler.py:151-345:
      * many policy-parameter sets x the same domains / init states): if group_size > 0, `weights` holds n_groups
-     * consecutive sets of n_weights floats and lane n of a sre_rollout launch evaluates set n / group_size.  Such
-     * policies read their set from global memory (no per-CTA staging, no tensor-core path). */
+     * consecutive sets of n_weights floats and lane n of a sre_rollout launch evaluates set n / group_size.  A
+     * group_size that is a multiple of the CTA size (128 with `precision` != FP32 on a [in,64,64,out] net, else 256;
+     * 128 for other shapes and the linear policy) runs the same kernels as a single set, one staged set per CTA;
+     * any other group_size reads the weights per lane from global memory. */
     int64_t group_size;
     int64_t n_groups;
 } sre_policy;

@@ -101,6 +101,7 @@ int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp) {
     SRE_CHECK_ARG(pol->group_size >= 0 && (pol->group_size == 0 || pol->n_groups >= 1), SRE_E_POLICY,
                   "group_size %lld / n_groups %lld invalid", (long long)pol->group_size, (long long)pol->n_groups);
     kp.group_size = pol->group_size;
+    kp.cta_groups = 0;  // decided per launch (launch_rollout)
     kp.n_layers = pol->n_layers;
     kp.n_feats = pol->n_feats;
     kp.hidden_nonlin = pol->hidden_nonlin;

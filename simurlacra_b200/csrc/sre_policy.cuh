@@ -19,6 +19,7 @@ struct KPolicy {
     long long n_weights;
     int smem_floats;  // size of the staged (re-laid-out) copy
     long long group_size;  // > 0: lane n uses weights + (n / group_size) * n_weights (parameter exploration)
+    int cta_groups;        // group_size is a multiple of the CTA size: one parameter set per CTA, staged like a single set
     int act_noise;    // SRE_ACT_NOISE_*
     float noise_scale[SRE_MAX_DA], noise_mean[SRE_MAX_DA];
 };
@@ -210,8 +211,8 @@ template <int IN, int HID, int OUT, bool FAST_TANH> struct FnnTiled {
 };
 
 // ---- generic FNN: any depth <= SRE_MAX_LAYERS, any width <= SRE_MAX_WIDTH; activations in local memory ----
-SRE_DEV void stage_generic(const KPolicy &pol, float *sm) {
-    for (long long i = threadIdx.x; i < pol.n_weights; i += blockDim.x) sm[i] = pol.weights[i];
+SRE_DEV void stage_generic(const KPolicy &pol, const float *w, float *sm) {
+    for (long long i = threadIdx.x; i < pol.n_weights; i += blockDim.x) sm[i] = w[i];
 }
 
 SRE_DEV void fnn_generic_forward(const KPolicy &pol, const float *sm, const float *obs, int n_obs, float *act,

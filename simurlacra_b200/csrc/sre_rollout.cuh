@@ -119,10 +119,14 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
     float *h1s = sm_w + Fast::W_FLOATS + warp * Fast::H1S_FLOATS;  // only meaningful for the tiled FNN variants
 
+    // parameter exploration with CTA-aligned groups: this CTA's parameter set is staged like a single set
+    const float *w_cta = pol.weights;
+    if (pol.cta_groups) w_cta += ((long long)blockIdx.x * blockDim.x / pol.group_size) * pol.n_weights;
+    const bool per_lane_w = pol.group_size > 0 && !pol.cta_groups;
     if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) +
-                              (io.traj ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0), pol.weights);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
-    else if (PV >= 16) Fast::stage(pol.weights, sm_w);
-    else if ((PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) && pol.group_size == 0) stage_generic(pol, sm_w);
+                              (io.traj ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0), w_cta);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
+    else if (PV >= 16) Fast::stage(w_cta, sm_w);
+    else if ((PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) && !per_lane_w) stage_generic(pol, w_cta, sm_w);
     __syncthreads();
 
     const long long N = io.n_envs;
@@ -315,7 +319,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
             else {
                 // parameter exploration: this lane's own parameter set, straight from global memory (L2-resident)
-                const float *wsrc = pol.group_size > 0 ? pol.weights + (valid ? n / pol.group_size : 0) * pol.n_weights : sm_w;
+                const float *wsrc = per_lane_w ? pol.weights + (valid ? n / pol.group_size : 0) * pol.n_weights : sm_w;
                 if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, wsrc, of, DO, af, DA);
                 else linear_forward<DO, DA>(pol, wsrc, of, af);
             }
@@ -460,15 +464,26 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
         pol.smem_floats = 0;
         return launch_rollout_pv<KIND, R, SRE_PV_ACTIONS>(cfg, distr, pol, io, stream);
     }
+    // parameter exploration: groups that are multiples of the variant's CTA size get one staged set per CTA and run
+    // every variant below unchanged; other group sizes read their weights per lane on the un-staged variants
+    auto cta_aligned = [&](int threads) { return pol.group_size > 0 && pol.group_size % threads == 0; };
+    pol.cta_groups = 0;
     if (pol.kind == SRE_POL_LINEAR) {
-        pol.smem_floats = pol.group_size > 0 ? 4 : (int)((pol.n_weights + 3) / 4 * 4);
+        pol.cta_groups = cta_aligned(LaunchShape<R, SRE_PV_LINEAR>::THREADS);
+        pol.smem_floats = (pol.group_size > 0 && !pol.cta_groups) ? 4 : (int)((pol.n_weights + 3) / 4 * 4);
         return launch_rollout_pv<KIND, R, SRE_PV_LINEAR>(cfg, distr, pol, io, stream);
     }
     // FNN: the register-resident fast path needs [do, H, H, da] with tanh hidden and linear output
     const bool two_hidden = pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
-    if (pol.group_size > 0) {  // per-lane parameter sets: only the un-staged forward passes apply
+    const int fast_threads = two_hidden && pol.sizes[1] == 64 && pol.precision != SRE_PREC_FP32 && sizeof(R) == 4
+                                 ? LaunchShape<R, SRE_PV_TC>::THREADS
+                                 : (two_hidden && (pol.sizes[1] == 64 || pol.sizes[1] == 32 || pol.sizes[1] == 16)
+                                        ? LaunchShape<R, SRE_PV_FNN16>::THREADS
+                                        : LaunchShape<R, SRE_PV_GENERIC>::THREADS);
+    pol.cta_groups = cta_aligned(fast_threads);
+    if (pol.group_size > 0 && !pol.cta_groups) {  // per-lane parameter sets: only the un-staged forward pass applies
         pol.smem_floats = 4;
         return launch_rollout_pv<KIND, R, SRE_PV_GENERIC>(cfg, distr, pol, io, stream);
     }

@@ -90,6 +90,35 @@ def test_grouped_launch_equals_one_launch_per_set(E, dtype):
                 assert float((g["state"][:, sl] - s["state"]).abs().max()) < 1e-3  # float32 policy on both builds
 
 
+@pytest.mark.parametrize("sizes,prec,R", [([6, 64, 64, 1], L.PREC_TF32X3, 128), ([6, 64, 64, 1], L.PREC_TF32X3, 384),
+                                          ([6, 64, 64, 1], L.PREC_FP32, 256), ([6, 16, 16, 1], L.PREC_FP32, 512),
+                                          ([6, 24, 1], L.PREC_FP32, 128), ([6, 64, 64, 1], L.PREC_TF32X3, 96)])
+def test_cta_aligned_groups_use_the_fast_variants(E, sizes, prec, R):
+    """Groups that are multiples of the CTA size stage one parameter set per CTA and run the tensor-core / tiled /
+    generic variants unchanged: bit-identical to one launch per set with that variant (R = 96 is not aligned and takes
+    the per-lane route: equal to round-off).  The last group is ragged."""
+    P, H = 5, 50
+    N = P * R - 40
+    cfg = E.make_cfg(L.QQ, 1 / 250.0, H, dtype=torch.float32, act_norm=True)
+    from simurlacra_b200.domain_randomization.default_randomizers import create_default_randomizer_qq
+
+    distr = create_default_randomizer_qq().table(QQubeSwingUpSim._param_names)
+    w = _sets(P, sizes, scale=0.2)
+    g = E.rollout(cfg, E.make_policy(L.POL_FNN, _t(w, torch.float32), sizes=sizes, precision=prec, group_size=R), N, H + 1,
+                  device=DEV, distr=distr, seed=4)
+    assert int(g["status"].max()) == 0
+    for p in range(P):
+        n = min(R, N - p * R)
+        s = E.rollout(cfg, E.make_policy(L.POL_FNN, _t(w[p], torch.float32), sizes=sizes, precision=prec), n, H + 1,
+                      device=DEV, distr=distr, seed=4, env_offset=p * R)
+        sl = slice(p * R, p * R + n)
+        if R % 128 == 0 and (R % 256 == 0 or prec != L.PREC_FP32 or len(sizes) == 3):
+            assert torch.equal(g["state"][:, sl], s["state"]) and torch.equal(g["ret"][sl], s["ret"])
+        else:
+            assert torch.equal(g["length"][sl], s["length"])
+            assert float((g["state"][:, sl] - s["state"]).abs().max()) < 1e-3
+
+
 def test_group_argument_errors(E):
     cfg = E.make_cfg(L.QQ, 1 / 250.0, 10, dtype=torch.float32)
     sizes = [6, 8, 1]

@@ -21,6 +21,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=osp.join(ROOT, "gpurun_out", "sweep.json"))
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--only", default="", help="comma-separated prefixes of the configs to run (e.g. F4)")
     args = ap.parse_args()
 
     import torch
@@ -42,7 +43,12 @@ def main():
     fma_peak = measure_fma_peak(E, L, torch, dev, L.F32)
     out["fp32_fma_peak_tflops"] = fma_peak
 
+    def want(name):
+        return not args.only or any(name.startswith(p) for p in args.only.split(","))
+
     def run(name, cfg, sizes, n, h, distr, precision, reps=3, record=False, flop=None, bytes_per_step=0):
+        if not want(name):
+            return
         w = torch.from_numpy(fnn_weights(sizes, seed=3)).to(dev)
         pol = E.make_policy(L.POL_FNN, w, sizes=sizes, precision=precision)
         kw = {}
@@ -106,6 +112,36 @@ def main():
         bytes_per_step=93)
     torch.cuda.empty_cache()
 
+    # ---- F4: parameter-exploration sampling, a population of policy-parameter sets in one launch ----
+    def run_pes(name, sizes, pop, per_set, precision, h=600, reps=3):
+        if not want(name):
+            return
+        nw = sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(len(sizes) - 1))
+        g = torch.Generator(device="cpu").manual_seed(1)
+        w = (torch.randn(pop, nw, generator=g) * 0.1).to(dev)
+        pol = E.make_policy(L.POL_FNN, w, sizes=sizes, precision=precision, group_size=per_set)
+        n = pop * per_set
+
+        def step(i):
+            return E.rollout(qq_cfg, pol, n, h + 1, device=dev, distr=qq_distr, seed=i, auto_reset=True)["stats"]
+
+        for i in range(2):
+            step(i)
+        t, st = time_launches(torch, lambda i: step(10 + i), reps, flush)
+        steps = sum(float(s[L.STAT_STEPS]) for s in st)
+        line = dict(config=name, envs=n, horizon=h, population=pop, rollouts_per_set=per_set,
+                    precision=["fp32_fma", "tcgen05_tf32x3", "tcgen05_tf32"][precision], env_steps_per_s=steps / t,
+                    ms_per_launch=1e3 * t / reps)
+        out["lines"].append(line)
+        print(json.dumps(line), flush=True)
+
+    run_pes("F4 PES qq+DR FNN[64,64] 8192 sets x 128 (one set per CTA, tcgen05)", [6, 64, 64, 1], 8192, 128, 1)
+    run_pes("F4 PES qq+DR FNN[64,64] 4096 sets x 256 (fp32 FMA)", [6, 64, 64, 1], 4096, 256, 0)
+    run_pes("F4 PES qq+DR FNN[16,16] 4096 sets x 256 (fp32 FMA)", [6, 16, 16, 1], 4096, 256, 0)
+    run_pes("F4 PES qq+DR FNN[16,16] 32768 sets x 32 (per-lane weights)", [6, 16, 16, 1], 32768, 32, 0)
+    run_pes("F4 PES qq+DR FNN[64,64] 16384 sets x 32 (per-lane weights)", [6, 64, 64, 1], 16384, 32, 0, reps=2)
+    run_pes("F4 PES qq+DR FNN[16,16] 131072 sets x 8 (per-lane weights)", [6, 16, 16, 1], 131072, 8, 0, reps=2)
+
     # ---- C5: differentiable cart-pole rollout, forward + adjoint through 300 steps, 256K envs ----
     n5, h5 = 1 << 18, 300
     dcfg = E.make_cfg(L.QCP, 1 / 20.0, h5, dtype=torch.float32, long_pole=True, wild_init=1)
@@ -122,6 +158,8 @@ def main():
         return E.qcp_diff_backward(dcfg, None, states, thdd, act, g_rew=g_rew)
 
     for name, fn in (("C5 qcp diff forward", fwd), ("C5 qcp diff forward+adjoint", fwd_bwd)):
+        if not want(name):
+            continue
         for i in range(2):
             fn(i)
         t, _ = time_launches(torch, lambda i: fn(i) and None, 5, flush)  # results dropped: no allocation in the timed region
