@@ -8,7 +8,7 @@ before each rollout.  Here the whole population is ONE launch of the rollout ker
 n // R, repetition n % R) with R = num_domains * num_init_states_per_domain; the parameter sets live in one
 [pop, num_param] float32 matrix on the device and each lane reads its own set (`sre_policy.group_size`).
 """
-from typing import List, NamedTuple, Optional, Sequence
+from typing import List, NamedTuple, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -22,6 +22,7 @@ from ..environment_wrappers.domain_randomization import (DomainRandWrapper, Doma
 from ..environment_wrappers.utils import inner_env, typed_env
 from ..environments.sim_base import SimEnv
 from ..policies.base import Policy
+from . import sharding
 from .rollout import compile_chain, rollout, sequences_from_records
 from .step_sequence import StepSequence
 
@@ -86,7 +87,7 @@ class ParameterExplorationSampler:
     """Parallel sampler for parameter exploration"""
 
     def __init__(self, env, policy: Policy, num_init_states_per_domain: int, num_domains: int, num_workers: int = 1,
-                 seed: Optional[int] = NO_SEED):
+                 seed: Optional[int] = NO_SEED, shard: Optional[Tuple[int, int]] = None):
         """
         :param env: environment to sample from; a DomainRandWrapper around it provides the domains
         :param policy: policy whose parameters are replaced by the sampled sets
@@ -94,6 +95,11 @@ class ParameterExplorationSampler:
         :param num_domains: number of domain-parameter sets per policy-parameter set
         :param num_workers: kept for the reference's signature (the batch dimension replaces the process pool)
         :param seed: base seed; rollout `i` of the `k`-th `sample()` call uses `(seed, k, i)` like the reference
+        :param shard: (rank, world_size) -- engine extension, one process per GPU: this process rolls out only its
+                      contiguous block of the parameter sets (no exchange during the horizon; domains, initial states
+                      and noise streams are keyed on the seed and the global lane index, so every split gives the same
+                      rollouts) and the mean returns are all-gathered afterwards.  Default: the initialised
+                      torch.distributed group, else (0, 1).  Needs an integer seed shared by all ranks.
         """
         if not isinstance(num_init_states_per_domain, int):
             raise pyrado.TypeErr(given=num_init_states_per_domain, expected_type=int)
@@ -113,6 +119,7 @@ class ParameterExplorationSampler:
         self.num_workers = num_workers
         self._seed = pyrado.get_base_seed() if seed is NO_SEED else seed
         self._sample_count = -1
+        self._shard = shard
 
     @property
     def num_rollouts_per_param(self) -> int:
@@ -181,9 +188,14 @@ class ParameterExplorationSampler:
         cc = compile_chain(self.env)
         sim = cc.sim if cc is not None else None
         desc = None
-        if cc is not None and np.isfinite(self.env.max_steps) and all(s is not None for s in init_states):
-            sets_dev = param_sets.detach().to(device=sim.device, dtype=torch.float32).contiguous()
+        rank, ws = self._shard if self._shard is not None else sharding.world()
+        lo, hi = sharding.shard_range(P, rank, ws)  # this rank's block of the population
+        if cc is not None and np.isfinite(self.env.max_steps) and all(s is not None for s in init_states) and hi > lo:
+            sets_dev = param_sets[lo:hi].detach().to(device=sim.device, dtype=torch.float32).contiguous()
             desc = self.policy.engine_desc(sim.device, param_sets=sets_dev, group_size=R)
+        if desc is None and ws > 1 and cc is not None:
+            raise pyrado.ValueErr(msg="Sharded parameter exploration needs a policy and a chain the kernels implement "
+                                      "and at least one parameter set per rank!")
         if desc is None:
             return self._sample_generic(param_sets, domain_params, init_states)
 
@@ -196,21 +208,29 @@ class ParameterExplorationSampler:
                     if k in sim._param_names:
                         prm[r, sim._param_names.index(k)] = float(np.asarray(v).reshape(-1)[0])
         ini = np.stack([np.asarray(s, dtype=np.float64).reshape(-1) for s in init_states])
-        to_dev = lambda a: torch.as_tensor(a, dtype=sim._dtype).to(sim.device).repeat(P, 1).contiguous()
+        Pl = hi - lo
+        to_dev = lambda a: torch.as_tensor(a, dtype=sim._dtype).to(sim.device).repeat(Pl, 1).contiguous()
         seed = pyrado.seed_hash(self._seed if isinstance(self._seed, int) else 0, self._sample_count, 0)
-        res = E.rollout(sim._make_cfg(cc.fusion), desc, P * R, int(sim.max_steps) + 1, device=sim.device,
-                        params=to_dev(prm), init=to_dev(ini), seed=seed, env_offset=0, episode=0, stop_on_done=True,
+        res = E.rollout(sim._make_cfg(cc.fusion), desc, Pl * R, int(sim.max_steps) + 1, device=sim.device,
+                        params=to_dev(prm), init=to_dev(ini), seed=seed, env_offset=lo * R, episode=0, stop_on_done=True,
                         auto_reset=False, record=return_rollouts, want_stats=False)
         st = int(res["status"].max())
         if st & (L.ST_NAN_OBS | L.ST_NAN_STATE):
             raise pyrado.ValueErr(msg="At least one observation value is NaN!")
         if st & L.ST_NAN_ACT:
             raise pyrado.ValueErr(msg="At least one action value is NaN!")
-        mean_ret = res["ret"].double().reshape(P, R).mean(dim=1).cpu().numpy()
-        ros = sequences_from_records(self.env, sim, res, float(sim.dt)) if return_rollouts else [None] * (P * R)
-        samples = [ParameterSample(params=param_sets[p], rollouts=ros[p * R:(p + 1) * R] if return_rollouts else [])
+        mean_ret = res["ret"].double().reshape(Pl, R).mean(dim=1)
+        if ws > 1 and self._shard is None:  # the only exchange: pop_size doubles, after the horizon
+            mean_ret = sharding.allgather_ragged(mean_ret, P)
+        elif ws > 1:  # explicit shard without a process group: the caller merges; foreign sets stay NaN
+            full = torch.full((P,), float("nan"), dtype=torch.float64, device=mean_ret.device)
+            full[lo:hi] = mean_ret
+            mean_ret = full
+        ros = sequences_from_records(self.env, sim, res, float(sim.dt)) if return_rollouts else []
+        samples = [ParameterSample(params=param_sets[p],
+                                   rollouts=ros[(p - lo) * R:(p - lo + 1) * R] if return_rollouts and lo <= p < hi else [])
                    for p in range(P)]
-        return ParameterSamplingResult(samples, mean_ret)
+        return ParameterSamplingResult(samples, mean_ret.cpu().numpy())
 
     def _sample_generic(self, param_sets, domain_params, init_states) -> ParameterSamplingResult:
         """Chains / policies the kernel cannot fuse: the reference's loop, one rollout() per (set, domain, init)."""

@@ -228,3 +228,72 @@ def test_sampler_generic_path():
     res = ParameterExplorationSampler(env, pol, num_init_states_per_domain=1, num_domains=2, seed=0).sample(sets)
     assert len(res) == 2 and res.num_rollouts == 4 and res.mean_returns.shape == (2,)
     assert res[0].rollouts[0].rollout_info["domain_param"] == res[1].rollouts[0].rollout_info["domain_param"]
+
+
+def test_population_shards_give_the_same_rollouts():
+    """Engine extension (one process per GPU): rank r of w rolls out its block of the parameter sets; mean returns and
+    rollouts of any split equal the unsharded call (lanes keyed on the global index, domains / init states on the seed)."""
+    env = _chain(max_steps=40)
+    torch.manual_seed(5)
+    pol = FNNPolicy(env.spec, hidden_sizes=[16, 16], hidden_nonlin=torch.tanh)
+    P = 7
+    sets = 0.4 * torch.randn(P, pol.num_param)
+    mk = lambda shard: ParameterExplorationSampler(env, pol, num_init_states_per_domain=2, num_domains=2, seed=11, shard=shard)
+    full = mk(None).sample(sets)
+    for ws in (2, 3):
+        merged = np.full(P, np.nan)
+        for rank in range(ws):
+            part = mk((rank, ws)).sample(sets)
+            own = ~np.isnan(part.mean_returns)
+            assert own.sum() in (P // ws, P // ws + 1) and np.isnan(merged[own]).all()
+            merged[own] = part.mean_returns[own]
+            for p in np.flatnonzero(own):
+                assert len(part[p].rollouts) == 4
+                for a, b in zip(part[p].rollouts, full[p].rollouts):
+                    np.testing.assert_array_equal(a.states, b.states)
+                    assert a.rollout_info["domain_param"] == b.rollout_info["domain_param"]
+            assert all(part[p].rollouts == [] for p in np.flatnonzero(~own))
+        np.testing.assert_array_equal(merged, full.mean_returns)
+
+
+_PES_WORKER = """
+import os, sys
+sys.path.insert(0, os.environ["SRE_ROOT"])
+import numpy as np, torch, torch.distributed as dist
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl")
+from simurlacra_b200.domain_randomization.default_randomizers import create_default_randomizer
+from simurlacra_b200.environment_wrappers import ActNormWrapper, DomainRandWrapperLive
+from simurlacra_b200.environments.pysim.quanser_qube import QQubeSwingUpSim
+from simurlacra_b200.policies import FNNPolicy
+from simurlacra_b200.sampling import ParameterExplorationSampler
+sim = QQubeSwingUpSim(dt=1 / 250.0, max_steps=40)
+env = DomainRandWrapperLive(ActNormWrapper(sim), create_default_randomizer(sim))
+torch.manual_seed(5)
+pol = FNNPolicy(env.spec, hidden_sizes=[16, 16], hidden_nonlin=torch.tanh)
+sets = 0.4 * torch.randn(9, pol.num_param)
+both = ParameterExplorationSampler(env, pol, 2, 2, seed=3).sample(sets, return_rollouts=False)        # sharded + all-gather
+alone = ParameterExplorationSampler(env, pol, 2, 2, seed=3, shard=(0, 1)).sample(sets, return_rollouts=False)
+assert not np.isnan(both.mean_returns).any()
+np.testing.assert_array_equal(both.mean_returns, alone.mean_returns)
+dist.barrier()
+sys.stdout.write(f"rank {dist.get_rank()} ok\\n")
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_population_sharding_over_nccl(tmp_path):
+    import os, socket, subprocess, sys
+
+    script = tmp_path / "worker.py"
+    script.write_text(_PES_WORKER)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                       capture_output=True, text=True, env=dict(os.environ, SRE_ROOT=root), timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
