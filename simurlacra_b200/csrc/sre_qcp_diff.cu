@@ -11,19 +11,34 @@
 
 namespace sre {
 
+// one state row (4 reals) as a single 128-bit access (float) or two (double); rows are 16-byte aligned because the
+// tape is a contiguous [H+1, N, 4] buffer whose base the C-ABI checks
+SRE_DEV void row4_store(float *p, const float *v) { *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+SRE_DEV void row4_store(double *p, const double *v) {
+    reinterpret_cast<double2 *>(p)[0] = make_double2(v[0], v[1]);
+    reinterpret_cast<double2 *>(p)[1] = make_double2(v[2], v[3]);
+}
+SRE_DEV void row4_load(const float *p, float *v) {
+    const float4 q = *reinterpret_cast<const float4 *>(p);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+}
+SRE_DEV void row4_load(const double *p, double *v) {
+    const double2 a = reinterpret_cast<const double2 *>(p)[0], b = reinterpret_cast<const double2 *>(p)[1];
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+
 template <typename R> struct QcpDiff {
     using E = Env<SRE_QCP, R>;
     using Cn = typename E::Consts;
 
     struct Stage {
-        R th, xd, thd, cin;
+        R xd, thd, cin, sn, cs;  // stage inputs; (sin, cos) of the stage angle are kept so the reverse pass reuses them
     };
 
     // reverse of E::accel: adjoints (gax, gat) of (xdd, thdd) -> adjoints of (th, xd, thd, u, cin), accumulated
     SRE_DEV static void accel_rev(const Cn &c, int flags, const Stage &st, R u, R gax, R gat, R &g_th, R &g_xd,
                                   R &g_thd, R &g_u, R &g_cin) {
-        R sn, cs;
-        m_sincos(st.th, sn, cs);
+        const R sn = st.sn, cs = st.cs;
         const bool simple = flags & SRE_F_SIMPLE_DYN;
         const bool dead = !simple && c.thold_neg <= u && u <= c.thold_pos;
         const R ue = dead ? (R)0 : u;
@@ -67,15 +82,17 @@ template <typename R> struct QcpDiff {
     SRE_DEV static void step_fwd(const Cn &c, R dt, int flags, const R *s, R c0, R u, R *sn_out, R &c_out,
                                  Stage *stg, R *ax, R *at) {
         const R dt2 = dt * (R)0.5;
-        stg[0] = Stage{s[1], s[2], s[3], c0};
-        E::accel(c, flags, stg[0].th, stg[0].xd, stg[0].thd, u, stg[0].cin, ax[0], at[0]);
+        stg[0].xd = s[2]; stg[0].thd = s[3]; stg[0].cin = c0;
+        m_sincos(s[1], stg[0].sn, stg[0].cs);
+        E::accel_sc(c, flags, stg[0].sn, stg[0].cs, stg[0].xd, stg[0].thd, u, stg[0].cin, ax[0], at[0]);
         R kx[4], kt[4];
         kx[0] = stg[0].xd + ax[0] * dt; kt[0] = stg[0].thd + at[0] * dt;
 #pragma unroll
         for (int i = 1; i < 4; i++) {
             const R h = (i < 3) ? dt2 : dt;
-            stg[i] = Stage{s[1] + h * kt[i - 1], s[2] + h * ax[i - 1], s[3] + h * at[i - 1], at[i - 1]};
-            E::accel(c, flags, stg[i].th, stg[i].xd, stg[i].thd, u, stg[i].cin, ax[i], at[i]);
+            stg[i].xd = s[2] + h * ax[i - 1]; stg[i].thd = s[3] + h * at[i - 1]; stg[i].cin = at[i - 1];
+            m_sincos(s[1] + h * kt[i - 1], stg[i].sn, stg[i].cs);
+            E::accel_sc(c, flags, stg[i].sn, stg[i].cs, stg[i].xd, stg[i].thd, u, stg[i].cin, ax[i], at[i]);
             kx[i] = stg[i].xd + ax[i] * dt;
             kt[i] = stg[i].thd + at[i] * dt;
         }
@@ -163,12 +180,10 @@ qcp_diff_forward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, co
     R st_lo[4], st_up[4], act_lo[1], act_up[1];
     qcp_load_consts<R>(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
     R s[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) s[i] = s0[n * 4 + i];
+    row4_load(s0 + n * 4, s);
     R carry = thdd0 ? thdd0[n] : (R)0;
     for (long long t = 0; t < H; t++) {
-#pragma unroll
-        for (int i = 0; i < 4; i++) states[(t * N + n) * 4 + i] = s[i];
+        row4_store(states + (t * N + n) * 4, s);
         thdd[t * N + n] = carry;
         const R a_un = act[t * N + n];
         const R u = m_min(m_max(a_un, act_lo[0]), act_up[0]);  // limit_act_clamp :282-284
@@ -188,8 +203,7 @@ qcp_diff_forward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, co
             done[t * N + n] = inside ? 0 : 1;
         }
     }
-#pragma unroll
-    for (int i = 0; i < 4; i++) states[(H * N + n) * 4 + i] = s[i];
+    row4_store(states + (H * N + n) * 4, s);
     thdd[H * N + n] = carry;
 }
 
@@ -211,8 +225,7 @@ qcp_diff_backward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, c
     lam_c = g_thdd ? g_thdd[H * N + n] : (R)0;
     for (long long t = H - 1; t >= 0; t--) {
         R s[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) s[i] = states[(t * N + n) * 4 + i];
+        row4_load(states + (t * N + n) * 4, s);
         const R carry = thdd[t * N + n];
         const R a_un = act[t * N + n];
         const bool in_range = (a_un >= act_lo[0]) && (a_un <= act_up[0]);
@@ -299,6 +312,7 @@ int sre_qcp_diff_forward(const sre_env_cfg *cfg, const void *params, const void 
     int e = qcp_check(cfg);
     if (e) return e;
     SRE_CHECK_ARG(s0 && act && states && thdd && n >= 0 && horizon >= 0, SRE_E_ARG, "NULL pointer or negative size");
+    SRE_CHECK_ARG(((uintptr_t)s0 | (uintptr_t)states) % 16 == 0, SRE_E_ARG, "s0 and states must be 16-byte aligned");
     if (n == 0) return 0;
     const unsigned blocks = (unsigned)((n + 127) / 128);
     cudaStream_t s = (cudaStream_t)stream;
@@ -326,6 +340,7 @@ int sre_qcp_diff_backward(const sre_env_cfg *cfg, const void *params, const void
     if (e) return e;
     SRE_CHECK_ARG(states && thdd && act && g_s0 && g_act && n >= 0 && horizon >= 0, SRE_E_ARG,
                   "NULL pointer or negative size");
+    SRE_CHECK_ARG((uintptr_t)states % 16 == 0, SRE_E_ARG, "states must be 16-byte aligned");
     if (n == 0) return 0;
     const unsigned blocks = (unsigned)((n + 127) / 128);
     cudaStream_t s = (cudaStream_t)stream;
