@@ -62,7 +62,7 @@ template <typename R> struct Env<SRE_QQ, R> {
         const R t1 = c.c1 * s2a * thd;  // shared by both Coriolis terms
         const R xx = c.k_u * u - c.k_thd * thd - (t1 * ald - c.c2 * sa * (ald * ald));
         const R yy = -c.Dp * ald - ((R)-0.5 * t1 * thd + c.c4 * sa);
-        const R inv = (R)1 / det;
+        const R inv = m_rcp(det);
         const R thdd = (c.c3 * xx - b * yy) * inv;
         const R aldd = (a * yy - b * xx) * inv;
         const R hdt2 = (R)0.5 * dt * dt;
@@ -158,7 +158,7 @@ template <typename R> struct Env<SRE_QCP, R> {
         const R r0 = f_tot - c.B_eq * xd - c.mpl * sn * thd2;
         const R r1 = -c.B_p * thd - c.mplg * sn;
         // 2x2 solve (np.linalg.solve :224 / torch.solve :422) by Cramer's rule
-        const R inv = (R)1 / (c.M00 * c.M11 - M01 * M01);
+        const R inv = m_rcp(c.M00 * c.M11 - M01 * M01);
         xdd = (c.M11 * r0 - M01 * r1) * inv;
         thdd = (c.M00 * r1 - M01 * r0) * inv;
     }
@@ -266,7 +266,7 @@ template <typename R> struct Env<SRE_QBB, R> {
         R sa, ca, sb, cb;
         m_sincos(h[0], sa, ca);
         m_sincos(h[1], sb, cb);
-        const R ica = (R)1 / ca, icb = (R)1 / cb;
+        const R ica = m_rcp(ca), icb = m_rcp(cb);
         const R a_dot = c.c_kin * thxd * cx * ica;
         const R b_dot = -c.c_kin * thyd * cy * icb;
         R xdd, ydd;

@@ -53,7 +53,7 @@ template <typename R> struct QcpDiff {
         const R M01 = c.mpl * cs;
         const R r0 = f_tot - c.B_eq * st.xd - c.mpl * sn * thd2;
         const R r1 = -c.B_p * st.thd - c.mplg * sn;
-        const R inv = (R)1 / (c.M00 * c.M11 - M01 * M01);
+        const R inv = m_rcp(c.M00 * c.M11 - M01 * M01);
         const R ax = (c.M11 * r0 - M01 * r1) * inv;
         const R at = (c.M00 * r1 - M01 * r0) * inv;
         // ---- reverse ----
