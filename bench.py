@@ -43,9 +43,9 @@ QQ_NAMES = ["gravity_const", "motor_resistance", "motor_back_emf", "mass_rot_pol
 FLOP_PER_STEP = {"qq": 120 + 9217, "qcp": 375 + 9089, "qbb": 260 + 2 * (8 * 16 + 16 * 16 + 16 * 2) + 34}
 RECORD_BYTES = {"qq": 53, "qcp": 53, "qbb": 93}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of rollout_kernel<QQ, float, tcgen05> at the default size
-# (2^20 envs x 600 steps), from the ncu --set full capture summarised in profiles/r01_m_final_rollout_qq_fnn64_1M.txt
-# (653 824 B read + 4 562 944 B written: returns, lengths, first-episode parameters; the state never leaves the registers)
-NCU_TRAFFIC = {(1 << 20, 600, 64, 1): 653824 + 4562944}
+# (2^20 envs x 600 steps), from the ncu --set full capture summarised in profiles/r01_n_final_rollout_qq_fnn64_1M.txt
+# (153 856 B read + 5 018 880 B written: returns, lengths, first-episode parameters; the state never leaves the registers)
+NCU_TRAFFIC = {(1 << 20, 600, 64, 1): 153856 + 5018880}
 
 
 def qq_randomizer(nom):
@@ -346,13 +346,13 @@ def main():
             t_iss = per_rank_rate * passes * 2 * hid * hid / 1e12
             roofline = dict(bound="tensor", achieved=achieved, peak=t_peak, unit="TFLOP/s", frac=achieved / t_peak,
                             traffic=NCU_TRAFFIC.get((N, H, hid, prec)),
-                            traffic_source="profiles/r01_m_final_rollout_qq_fnn64_1M.txt (bytes per launch)", flop_per_env_step=flop, issued=t_iss, frac_issued=t_iss / t_peak,
+                            traffic_source="profiles/r01_n_final_rollout_qq_fnn64_1M.txt (bytes per launch)", flop_per_env_step=flop, issued=t_iss, frac_issued=t_iss / t_peak,
                             peak_source=f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}) / 2: kind::tf32 "
                                         f"runs at half the bf16 rate",
                             note=f"{passes} tcgen05.mma kind::tf32 pass(es) per 64x64 layer (3xTF32 split keeps fp32-level "
                                  f"accuracy); per env-step only 8192 of {flop} FLOP are GEMM-shaped, the rest (layer 1, "
                                  f"128 tanh, layer 3, dynamics, sincos, reward) runs on the CUDA cores: ncu shows issue "
-                                 f"slots 56% and the MUFU pipe 51% busy, tensor pipe 24% (profiles/r01_m_*), so the "
+                                 f"slots 56% and the MUFU pipe 51% busy, tensor pipe 24% (profiles/r01_n_*), so the "
                                  f"kernel is CUDA-core/MUFU bound -- see roofline_fp32")
             extras["roofline_fp32"] = fp32_roof
         else:
