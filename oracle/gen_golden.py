@@ -420,10 +420,109 @@ def gen_wrappers():
     print("wrappers_reference.npz", {k: v.shape for k, v in out.items() if k.endswith("_obs")})
 
 
+def gen_calm_trajs():
+    """north_star's fp32 bar (1e-4 over the FULL 600-step horizon, lengths bit-exact) needs cases where the swing-up
+    pendulums are NOT chaotic: small voltages (|a| <= 0.5 V) about the hanging equilibrium, nominal and randomized
+    parameters.  Same file format as gen_env_trajs."""
+    for name, kw in (("qq-su", {}), ("qcp-su", dict(wild_init="False")), ("qcp-su", dict(wild_init="False", simple_dynamics=True))):
+        rng = np.random.RandomState(4321 + sum(map(ord, name)) + int(bool(kw.get("simple_dynamics"))))
+        cases, keys = {}, None
+        n_cases = 4
+        for c in range(n_cases):
+            env = make_env(name, **kw)
+            H = env.max_steps
+            dp = None
+            if c % 2 == 1:
+                pyrado.set_seed(200 + c)
+                rz = RANDOMIZERS[name]()
+                rz.randomize(1)
+                dp = {k: float(v) for k, v in rz.get_params(fmt="dict", dtype="numpy").items()}
+            pyrado.set_seed(50 + c)
+            if dp is not None:
+                env.domain_param = dp
+            init = env.init_space.sample_uniform()  # qq: +-[2, 1, .5, .5] deg about hanging; qcp 'False' box
+            amp = [0.5, 0.3, 0.5, 0.1][c]
+            actions = rng.uniform(-1, 1, size=(H, 1)) * amp
+            if c >= 2:  # slow piecewise-constant component
+                seg = rng.uniform(-1, 1, size=(H // 50 + 1, 1)) * amp
+                actions = 0.4 * actions + 0.6 * np.repeat(seg, 50, axis=0)[:H]
+            tr = run_traj(env, init, actions, dp)
+            keys, pv = param_vector(env)
+            cases[f"c{c}_init"] = np.asarray(init, dtype=np.float64)
+            cases[f"c{c}_params"] = pv
+            cases[f"c{c}_actions"] = actions[: tr["length"]]
+            for k, v in tr.items():
+                cases[f"c{c}_{k}"] = np.asarray(v)
+            lo_s, up_s = env.state_space.bounds
+            lo, up = env.act_space.bounds
+            cases[f"c{c}_state_lo"], cases[f"c{c}_state_up"] = lo_s, up_s
+            cases[f"c{c}_act_lo"], cases[f"c{c}_act_up"] = lo, up
+            print(f"  {name} calm case {c}: length {tr['length']}/{H} ret {tr['rews'].sum():.6g} max|s| "
+                  f"{np.abs(tr['states']).max(0)} randomized={dp is not None}")
+        cases["n_cases"] = np.array(n_cases)
+        cases["param_keys"] = np.array(keys)
+        cases["dt"] = np.array(env.dt)
+        cases["max_steps"] = np.array(env.max_steps)
+        suffix = "_simple" if kw.get("simple_dynamics") else ""
+        np.savez_compressed(osp.join(OUT, f"traj_{name}_calm{suffix}.npz"), **cases)
+
+
+def gen_fnn_closed_loop_envs():
+    """FNN [do, 64, 64, da] tanh in closed loop on the reference (torch float32 policy on the CPU, numpy float64 env)
+    for QQube, QCartPole, QBallBalancer and Pendulum: the golden cases of the tensor-core policy path.  The output
+    layer keeps its default (small) initialisation scaled so that the systems move but stay well conditioned."""
+    from pyrado.policies.feed_back.fnn import FNN
+
+    out = {}
+    specs = (("qq", lambda: QQubeSwingUpSim(dt=1 / 250.0, max_steps=600), False, 2.0),
+             ("qq_norm", lambda: QQubeSwingUpSim(dt=1 / 250.0, max_steps=600), True, 0.25),
+             ("qcp", lambda: QCartPoleSwingUpSim(dt=1 / 250.0, max_steps=600, long=True, wild_init="False"), True, 25.0),
+             ("qbb", lambda: QBallBalancerSim(dt=0.01, max_steps=500), True, 0.5),
+             ("pend", lambda: PendulumSim(dt=1 / 50.0, max_steps=400, init_state=np.array([0.3, -0.2])), False, 1.0))
+    for i, (tag, mk, wrap, gain) in enumerate(specs):
+        pyrado.set_seed(10 + i)
+        env = mk()
+        n_in, n_out = env.obs_space.flat_dim, env.act_space.flat_dim
+        net = FNN(input_size=n_in, output_size=n_out, hidden_sizes=[64, 64], hidden_nonlin=torch.tanh)
+        with torch.no_grad():
+            net.output_layer.weight.mul_(gain)
+        wenv = ActNormWrapper(env) if wrap else env
+        init = env.init_space.sample_uniform()
+        o = wenv.reset(init_state=init.copy())
+        obs = np.asarray(env.observe(env.state), dtype=np.float64) if tag.startswith("qcp") else np.asarray(o, dtype=np.float64)
+        states, obss, acts, rews, hid = [env.state.copy()], [obs.copy()], [], [], [hidden_of(env)]
+        done = False
+        while not done:
+            with torch.no_grad():
+                a = net(torch.from_numpy(obs).to(torch.get_default_dtype())).numpy().astype(np.float64)
+            o, r, done, _ = wenv.step(a)
+            obs = np.asarray(o, dtype=np.float64)
+            states.append(env.state.copy()); obss.append(obs.copy()); acts.append(a); rews.append(r); hid.append(hidden_of(env))
+        params = []
+        for layer in list(net.hidden_layers) + [net.output_layer]:
+            params += [layer.weight.detach().numpy().reshape(-1), layer.bias.detach().numpy().reshape(-1)]
+        out[f"{tag}_weights"] = np.concatenate(params).astype(np.float32)
+        out[f"{tag}_sizes"] = np.array([n_in, 64, 64, n_out])
+        out[f"{tag}_init"] = np.asarray(init, dtype=np.float64)
+        out[f"{tag}_states"] = np.array(states)
+        out[f"{tag}_hidden"] = np.array(hid)
+        out[f"{tag}_obs"] = np.array(obss)
+        out[f"{tag}_acts"] = np.array(acts)
+        out[f"{tag}_rews"] = np.array(rews)
+        out[f"{tag}_actnorm"] = np.array(wrap)
+        out[f"{tag}_dt"] = np.array(env.dt)
+        out[f"{tag}_max_steps"] = np.array(env.max_steps)
+        print(f"  fnn64 {tag}: length {len(rews)} ret {np.sum(rews):.6g} max|a| {np.abs(acts).max():.3g} "
+              f"max|s| {np.abs(np.array(states)).max(0)}")
+    out["tags"] = np.array([s[0] for s in specs])
+    np.savez_compressed(osp.join(OUT, "fnn64_closed_loop_envs.npz"), **out)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
         {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6),
-         "wrappers": gen_wrappers, "bob-d": lambda: gen_env_trajs("bob-d", n_cases=6)}[sys.argv[1]]()
+         "wrappers": gen_wrappers, "bob-d": lambda: gen_env_trajs("bob-d", n_cases=6), "calm": gen_calm_trajs,
+         "fnn64": gen_fnn_closed_loop_envs, "dr": gen_dr_moments}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)
@@ -441,5 +540,9 @@ if __name__ == "__main__":
     print("stab"); gen_stab_envs()
     print("returns"); gen_returns()
     print("pend"); gen_env_trajs("pend", n_cases=6)
+    print("bob-d"); gen_env_trajs("bob-d", n_cases=6)
+    print("wrappers"); gen_wrappers()
+    print("calm"); gen_calm_trajs()
+    print("fnn64"); gen_fnn_closed_loop_envs()
     sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
     print(f"golden size: {sz / 1e6:.2f} MB")

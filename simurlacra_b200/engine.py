@@ -147,10 +147,13 @@ def make_distr_table(entries: Sequence[dict]):
 
 
 def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), feats=(), hidden_nonlin: int = 0,
-                output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = 0, act_noise: int = 0,
+                output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = L.PREC_TF32X3, act_noise: int = 0,
                 act_noise_scale=(), act_noise_mean=(), group_size: int = 0) -> L.Policy:
     """`group_size` > 0: `weights` is a [n_sets, n_weights] matrix of parameter sets and lane n of a rollout launch
-    evaluates set n // group_size (parameter-exploration sampling)."""
+    evaluates set n // group_size (parameter-exploration sampling).
+    `precision`: arithmetic of a [in, 64, 64, out] tanh network's hidden layer in the float32 build -- L.PREC_TF32X3
+    (default, tcgen05 3 x TF32 split, fp32-level accuracy), L.PREC_FP32 (CUDA-core FMA), L.PREC_TF32 (single pass);
+    other shapes and the float64 build ignore it."""
     p = L.Policy()
     set_act_noise(p, act_noise, act_noise_scale, act_noise_mean)
     p.kind = kind

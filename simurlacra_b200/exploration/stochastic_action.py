@@ -63,7 +63,7 @@ class StochasticActionExplStrat(Policy, ABC):
     def engine_precision(self):
         """Arithmetic of the fused hidden layer: the wrapped policy's setting"""
         pol = self.__dict__.get("_modules", {}).get("policy")
-        return pol.engine_precision if pol is not None else L.PREC_FP32
+        return pol.engine_precision if pol is not None else L.PREC_TF32X3
 
     @engine_precision.setter
     def engine_precision(self, value):

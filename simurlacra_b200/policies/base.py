@@ -40,10 +40,12 @@ class Policy(nn.Module, ABC):
         if use_cuda and not torch.cuda.is_available():
             warn("Tried to run on CUDA, but it is not available. Falling back to CPU.")
         self._device = "cuda" if use_cuda and torch.cuda.is_available() else "cpu"
-        # arithmetic of the fused hidden layer (engine extension): L.PREC_FP32 (CUDA-core FMA, default),
-        # L.PREC_TF32X3 (tcgen05 tensor cores, 3 x TF32 split, fp32-level accuracy) or L.PREC_TF32
-        self.engine_precision = L.PREC_FP32
+        # arithmetic of the fused hidden layer (engine extension): L.PREC_TF32X3 (default: tcgen05 tensor cores with the
+        # 3 x TF32 split, fp32-level accuracy; applies to float32 [in, 64, 64, out] tanh networks, every other shape and
+        # the float64 build run the CUDA-core FMA path whatever this says), L.PREC_FP32 (CUDA-core FMA) or L.PREC_TF32
+        self.engine_precision = L.PREC_TF32X3
         self._pinned = None
+        self._pinned_free = None  # CUDA event: the last H2D copy out of the pinned staging buffer has completed
         self._dev_weights = {}
 
     @property
@@ -121,11 +123,18 @@ class Policy(nn.Module, ABC):
             device = torch.device(device)
             if self._pinned is None or self._pinned.numel() != v.numel():
                 self._pinned = torch.empty(v.numel(), dtype=torch.float32).pin_memory()
+                self._pinned_free = None
+            if self._pinned_free is not None:
+                # an earlier asynchronous copy may still be queued behind a rollout launch: the staging buffer must not
+                # change under it (the earlier launch would silently run with these later weights)
+                self._pinned_free.synchronize()
             self._pinned.copy_(v)
             dev = self._dev_weights.get(device)
             if dev is None or dev.numel() != v.numel():
                 dev = self._dev_weights[device] = torch.empty(v.numel(), dtype=torch.float32, device=device)
             dev.copy_(self._pinned, non_blocking=True)
+            self._pinned_free = torch.cuda.Event()
+            self._pinned_free.record(torch.cuda.current_stream(device))
             return dev
 
     def forward_engine(self, obs: torch.Tensor) -> torch.Tensor:

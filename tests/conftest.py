@@ -48,7 +48,16 @@ ENV_FILES = [
     ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st")),
     ("traj_qcp-st_simple", "qcp-su", dict(long_pole=True, simple_dynamics=True, stab="qcp-st")),
     ("traj_bob-d", "bob", dict(disc_act=True)),  # BallOnBeamDiscSim: actions projected onto {-max, 0, +max}
+    # non-chaotic regime of the swing-up pendulums: |a| <= 0.5 V about the hanging equilibrium, 600 steps (north_star's
+    # fp32 bar -- 1e-4 over the FULL horizon, bit-exact lengths -- is asserted on these)
+    ("traj_qq-su_calm", "qq-su", {}),
+    ("traj_qcp-su_calm", "qcp-su", dict(long_pole=True)),
+    ("traj_qcp-su_calm_simple", "qcp-su", dict(long_pole=True, simple_dynamics=True)),
 ]
+
+# closed-loop FNN [do, 64, 64, da] goldens (tests/golden/fnn64_closed_loop_envs.npz): tag -> (kind name, oracle kwargs)
+FNN64_CASES = {"qq": ("qq-su", {}), "qq_norm": ("qq-su", {}), "qcp": ("qcp-su", dict(long_pole=True)), "qbb": ("qbb", {}),
+               "pend": ("pend", {})}
 
 # task_args defaults of the stabilisation envs: quanser_qube.py:223-229 (ExpQuadrErrRewFcn), quanser_cartpole.py:491-500
 # (QuadrErrRewFcn inside FinalRewTask(state_dependent, time_dependent)); RadiallySymmDesStateTask idcs=[1] in both

@@ -124,7 +124,10 @@ def test_trajectory_fp64_matches_reference(E, fname, kind_name, kw):
 FP32_TOL = {"traj_omo": (1e-4, None), "traj_bob": (1e-4, None), "traj_qbb": (1e-4, None), "traj_qbb_simple": (1e-4, None),
             "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100),
             "traj_pend": (1e-4, None), "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50),
-            "traj_bob-d": (1e-4, None)}
+            "traj_bob-d": (1e-4, None),
+            # the swing-up pendulums in their non-chaotic regime: north_star's bar over the FULL horizon
+            "traj_qq-su_calm": (1e-4, None), "traj_qcp-su_calm": (1e-4, None), "traj_qcp-su_calm_simple": (1e-4, None)}
+EXACT_LENGTH_FP32 = ("traj_qq-su_calm", "traj_qcp-su_calm", "traj_qcp-su_calm_simple")
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", ENV_FILES)
@@ -138,10 +141,49 @@ def test_trajectory_fp32(E, fname, kind_name, kw):
         Tn = int(g[f"c{c}_length"])
         n = min(Tn, upto) if upto else Tn
         Tl = int(res["length"][0])
-        if upto is None:
+        if fname in EXACT_LENGTH_FP32:
+            assert Tl == Tn, (fname, c, Tl, Tn)  # episode lengths bit-exact (north_star)
+        elif upto is None:
             assert abs(Tl - Tn) <= 1  # a bound crossing may move by one step in fp32
         m = min(n, Tl)
         st = res["state"][: m + 1, 0].double().cpu().numpy()
         err = np.abs(st - S[: m + 1]) / np.maximum(1.0, np.abs(S[: m + 1]))
         worst = max(worst, err.max())
     assert worst < tol, (fname, worst)
+
+
+@pytest.mark.parametrize("fname,kind_name,kw", [e for e in ENV_FILES if FP32_TOL[e[0]][1] is not None])
+def test_fp64_sensitivity_of_the_golden_cases(E, fname, kind_name, kw):
+    """Why the large-action swing-up / stabilisation cases are compared over their first 50-100 steps only in float32:
+    the fp64 build's OWN sensitivity.  Every case is run twice in fp64, the second time with the initial state moved by
+    1e-9 (relative to the state scale); g(t) = |delta s(t)| / 1e-9 is the amplification of a perturbation.  A float32
+    trajectory carries a per-step rounding error of ~6e-8 of the state scale, so its distance to the fp64 reference is
+    bounded by ~6e-8 * sum_t g -- the test asserts (a) that the float32 build stays within 1e-4 wherever that bound is
+    below 1e-4 (i.e. the float32 error is explained by conditioning, not by the kernel), and (b) that the cases really
+    are ill-conditioned beyond the compared window (amplification > 1e3 somewhere), which is why 1e-4 over the full
+    horizon is asserted on the `_calm` cases instead."""
+    g = golden(fname)
+    amp_max = 0.0
+    for c in range(int(g["n_cases"])):
+        Tn = int(g[f"c{c}_length"])
+        S = g[f"c{c}_states"]
+        scale = np.maximum(1.0, np.abs(S).max(0))
+        base = _rollout_case(E, g, c, kind_name, kw, torch.float64)
+        g2 = {k: g[k] for k in g.files}
+        eps = 1e-9
+        g2[f"c{c}_init"] = g[f"c{c}_init"] + eps * scale  # all of these envs take a full-state init (ds = 4)
+        pert = _rollout_case(E, g2, c, kind_name, kw, torch.float64)
+        m = min(Tn, int(pert["length"][0]), int(base["length"][0]))
+        ds = (np.abs(pert["state"][: m + 1, 0].cpu().numpy() - base["state"][: m + 1, 0].cpu().numpy()) / scale).max(1)
+        gt = ds / eps
+        amp_max = max(amp_max, gt.max())
+        bound = 6e-8 * np.cumsum(gt)
+        f32 = _rollout_case(E, g, c, kind_name, kw, torch.float32)
+        m32 = min(m, int(f32["length"][0]))
+        e32 = (np.abs(f32["state"][: m32 + 1, 0].double().cpu().numpy() - S[: m32 + 1]) / np.maximum(1.0, np.abs(S[: m32 + 1]))).max(1)
+        well = bound[: m32 + 1] < 1e-4
+        print(f"{fname} c{c}: max amplification {gt.max():.3g} at step {int(gt.argmax())}, well-conditioned steps "
+              f"{int(well.sum())}/{m32 + 1}, fp32 err there {e32[well].max() if well.any() else 0:.2e}, overall {e32.max():.2e}")
+        if well.any():
+            assert e32[well].max() < 1e-4, (fname, c, e32[well].max())
+    assert amp_max > 1e3, (fname, amp_max)

@@ -7,6 +7,8 @@ import numpy as np
 import pytest
 import torch
 
+from conftest import FNN64_CASES, golden
+
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
@@ -125,3 +127,82 @@ def test_rollout_tensor_core_auto_reset_statistics(E):
     pol = E.make_policy(L.POL_FNN, wd, sizes=sizes, precision=L.PREC_TF32X3)
     r = E.rollout(cfg, pol, 777, H + 1, device=DEV, distr=_qq_distr(E), seed=2, record=False)
     assert int(r["length"].min()) >= 1 and int(r["length"].max()) <= H
+
+
+# ---- the tensor-core rollout kernel against the REFERENCE and the ORACLE (not against the repo's own FMA path) --------
+PRECS = {"fp32_fma": 0, "tf32x3": 1}
+
+
+@pytest.mark.parametrize("tag", list(FNN64_CASES))
+@pytest.mark.parametrize("prec", list(PRECS))
+def test_fnn64_closed_loop_golden(E, tag, prec):
+    """FNN [do, 64, 64, da] in closed loop on QQube / QCartPole / QBallBalancer / Pendulum: the float32 production build
+    (CUDA-core FMA and tcgen05 3 x TF32 hidden layer) against the run of the UNMODIFIED reference (torch float32 policy
+    on the CPU, numpy float64 env; tests/golden/fnn64_closed_loop_envs.npz): states, observations and actions within
+    1e-4 over the whole episode, episode length equal."""
+    g = golden("fnn64_closed_loop_envs")
+    kind_name, kw = FNN64_CASES[tag]
+    kind = E.KIND_BY_NAME[kind_name]
+    sizes = [int(s) for s in g[f"{tag}_sizes"]]
+    S, O, A = g[f"{tag}_states"], g[f"{tag}_obs"], g[f"{tag}_acts"]
+    H, ms = S.shape[0] - 1, int(g[f"{tag}_max_steps"])
+    cfg = E.make_cfg(kind, float(g[f"{tag}_dt"]), ms, dtype=torch.float32, act_norm=bool(g[f"{tag}_actnorm"]), **kw)
+    wd = torch.from_numpy(g[f"{tag}_weights"]).to(DEV)
+    pol = E.make_policy(E_L().POL_FNN, wd, sizes=sizes, precision=PRECS[prec])
+    init = torch.as_tensor(g[f"{tag}_init"][None, :], dtype=torch.float32).to(DEV).contiguous()
+    res = E.rollout(cfg, pol, 1, ms + 1, device=DEV, init=init)
+    assert int(res["length"][0]) == H, (tag, prec, int(res["length"][0]), H)
+    st = res["state"][: H + 1, 0].double().cpu().numpy()
+    ob = res["obs"][: H + 1, 0].double().cpu().numpy()
+    ac = res["act"][:H, 0].double().cpu().numpy()
+    es = (np.abs(st - S) / np.maximum(1.0, np.abs(S))).max()
+    eo = (np.abs(ob - O) / np.maximum(1.0, np.abs(O))).max()
+    ea = (np.abs(ac - A) / np.maximum(1.0, np.abs(A))).max()
+    print(f"fnn64 {tag} {prec}: max rel err state {es:.2e} obs {eo:.2e} act {ea:.2e} over {H} steps")
+    assert es < 1e-4 and eo < 1e-4 and ea < 1e-4, (tag, prec, es, eo, ea)
+    np.testing.assert_allclose(res["rew"][:H, 0].double().cpu().numpy(), g[f"{tag}_rews"], rtol=1e-4, atol=1e-5)
+    assert int(res["status"][0]) == 0
+
+
+def E_L():
+    from simurlacra_b200 import _lib as L
+
+    return L
+
+
+@pytest.mark.parametrize("kind_name,dt,H,kw", [("qq-su", 1 / 250.0, 600, {}), ("qcp-su", 1 / 250.0, 600, dict(long_pole=True)),
+                                               ("qbb", 0.01, 500, {}), ("pend", 1 / 50.0, 400, {})])
+@pytest.mark.parametrize("prec", list(PRECS))
+def test_rollout_fp32_fnn64_matches_oracle(E, orc, kind_name, dt, H, kw, prec):
+    """float32 twin of test_gpu_engine.py::test_rollout_fp64_matches_oracle for the [64, 64] policy: the whole fused path
+    of the PRODUCTION build (sampled init states + ActNorm + FNN [do, 64, 64, da] + step + records) against the fp64
+    oracle on the same seeded inputs, per step, for both arithmetics of the hidden layer.  Small policy weights keep the
+    closed loops in their well-conditioned regime (see test_fp64_sensitivity_of_the_golden_cases for the other one)."""
+    L = E_L()
+    kind = E.KIND_BY_NAME[kind_name]
+    d = E.dims(kind)
+    N, Hs = 256, min(H, 200)
+    lp = kw.get("long_pole", False)
+    sizes = [d["do"], 64, 64, d["da"]]
+    w = _weights(sizes, seed=17, scale=0.08)
+    cfg = E.make_cfg(kind, dt, Hs, dtype=torch.float32, act_norm=True, **kw)
+    pol = E.make_policy(L.POL_FNN, torch.from_numpy(w).to(DEV), sizes=sizes, precision=PRECS[prec])
+    res = E.rollout(cfg, pol, N, Hs + 1, device=DEV, seed=23, env_offset=5)
+    ref = orc.rollout_batch(kind, dt, Hs, N, Hs, policy=orc.make_policy(orc.POL_FNN, w, sizes=sizes), long_pole=lp,
+                            act_norm=True, seed=23, env_offset=5)
+    ln = res["length"].cpu().numpy()
+    same = ln == ref["length"]
+    assert same.mean() >= 0.99 and np.abs(ln - ref["length"]).max() <= 1, (same.mean(), np.abs(ln - ref["length"]).max())
+    st, ob, ac, rw = (res[k].double().cpu().numpy() for k in ("state", "obs", "act", "rew"))
+    worst = np.zeros(N)
+    for n in np.nonzero(same)[0]:
+        T = ln[n]
+        es = (np.abs(st[: T + 1, n] - ref["state"][: T + 1, n]) / np.maximum(1.0, np.abs(ref["state"][: T + 1, n]))).max()
+        eo = (np.abs(ob[: T + 1, n] - ref["obs"][: T + 1, n]) / np.maximum(1.0, np.abs(ref["obs"][: T + 1, n]))).max()
+        ea = (np.abs(ac[:T, n] - ref["act"][:T, n]) / np.maximum(1.0, np.abs(ref["act"][:T, n]))).max()
+        er = np.abs(rw[:T, n] - ref["rew"][:T, n]).max()
+        worst[n] = max(es, eo, ea, er)
+    print(f"fp32 fnn64 {kind_name} {prec}: worst lane {worst.max():.2e}, median {np.median(worst):.2e}, same length "
+          f"{same.mean():.4f}")
+    assert worst.max() < 1e-4, (kind_name, prec, worst.max())
+    np.testing.assert_allclose(res["ret"].double().cpu().numpy()[same], ref["ret"][same], rtol=1e-4, atol=1e-4)

@@ -8,7 +8,7 @@ All CPU, runs in seconds.
 import numpy as np
 import pytest
 
-from conftest import ENV_FILES, OMO_TASK, STAB_TASKS, golden
+from conftest import ENV_FILES, FNN64_CASES, OMO_TASK, STAB_TASKS, golden
 
 
 def _make(O, kind_name, dt, max_steps, kw):
@@ -114,6 +114,27 @@ def test_fnn_closed_loop(orc):
         assert err.max() < 1e-4, (tag, err.max())
         np.testing.assert_allclose(res["rew"][:H, 0], g[f"{tag}_rews"], rtol=1e-4, atol=1e-6)
         np.testing.assert_allclose(res["act"][:H, 0], g[f"{tag}_acts"], rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("tag", list(FNN64_CASES))
+def test_fnn64_closed_loop_envs(orc, tag):
+    """FNN [do, 64, 64, da] in closed loop on QQube / QCartPole / QBallBalancer / Pendulum against the reference run
+    (torch float32 policy, numpy float64 env): states 1e-4 over the whole episode, lengths equal."""
+    g = golden("fnn64_closed_loop_envs")
+    kind_name, kw = FNN64_CASES[tag]
+    kind = orc.KIND_BY_NAME[kind_name]
+    sizes = [int(s) for s in g[f"{tag}_sizes"]]
+    pol = orc.make_policy(orc.POL_FNN, g[f"{tag}_weights"], sizes=sizes)
+    S = g[f"{tag}_states"]
+    H, ms = S.shape[0] - 1, int(g[f"{tag}_max_steps"])
+    init = g[f"{tag}_init"][None, :]
+    res = orc.rollout_batch(kind, float(g[f"{tag}_dt"]), ms, 1, ms, policy=pol, act_norm=bool(g[f"{tag}_actnorm"]),
+                            init=init, **kw)
+    assert int(res["length"][0]) == H
+    err = np.abs(res["state"][: H + 1, 0] - S) / np.maximum(1.0, np.abs(S))
+    assert err.max() < 1e-4, (tag, err.max())
+    np.testing.assert_allclose(res["rew"][:H, 0], g[f"{tag}_rews"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(res["obs"][: H + 1, 0], g[f"{tag}_obs"], rtol=1e-4, atol=1e-4)
 
 
 @pytest.mark.parametrize("simple", [False, True])
