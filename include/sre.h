@@ -114,6 +114,12 @@ extern "C" {
 #define SRE_ST_NAN_ACT 2   /* sampling/rollout.py:223 would raise ValueErr */
 #define SRE_ST_NAN_OBS 4   /* sampling/rollout.py:193 would raise ValueErr */
 
+/* curr_step words of the step-granular API: the step count sits in the low 30 bits; bit 30 says that the episode's
+ * FinalRewTask has already yielded its final reward (tasks/final_reward.py:131-135: once per episode).  sre_reset
+ * clears the word, sre_step maintains both parts. */
+#define SRE_STEP_YIELDED_FINAL (1 << 30)
+#define SRE_STEP_COUNT_MASK 0x3FFFFFFF
+
 /* error codes */
 #define SRE_E_ARG (-1)
 #define SRE_E_KIND (-2)
@@ -286,7 +292,8 @@ int sre_reset(const sre_env_cfg *cfg, const void *params, const void *init, int 
               void *state, void *hidden, int32_t *curr_step, void *obs, uint64_t seed, uint64_t env_offset,
               uint32_t episode, int64_t n, void *stream);
 /* act real [N, da] in the units of the outermost fused wrapper (normalised if cfg.act_norm).
- * Updates state/hidden/curr_step in place; writes obs [N, do], rew [N], done uint8 [N], status int32 [N].
+ * Updates state/hidden/curr_step in place (curr_step: count | SRE_STEP_YIELDED_FINAL, see above); writes obs [N, do],
+ * rew [N], done uint8 [N], status int32 [N].
  * noise_seed/env_offset/episode key the observation noise when cfg.obs_noise. */
 int sre_step(const sre_env_cfg *cfg, const void *params, const void *act, void *state, void *hidden,
              int32_t *curr_step, void *obs, void *rew, uint8_t *done, int32_t *status, uint64_t seed,

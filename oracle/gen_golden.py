@@ -365,6 +365,19 @@ def gen_returns():
         out[f"c{c}_adv"] = np.asarray(gae_returns(ro, gamma, lamb), dtype=np.float64).copy()
         print(f"  returns case {c}: n={n} G0={out[f'c{c}_ret'][0]:.6g} A0={out[f'c{c}_adv'][0]:.6g}")
     out["n_cases"] = np.array(len(cases))
+    # discounted_values over SEVERAL rollouts (step_sequence.py:1075-1090): one 1-D tensor for 'torch', one row per
+    # rollout for 'numpy'
+    from pyrado.sampling.step_sequence import discounted_values
+
+    for tag, lens in (("eq", (5, 5, 5)), ("ragged", (4, 7, 3))):
+        ros = [StepSequence(rewards=rng.randn(n), observations=rng.randn(n + 1, 2), actions=rng.randn(n, 1), complete=True)
+               for n in lens]
+        out[f"dvs_{tag}_lens"] = np.array(lens)
+        out[f"dvs_{tag}_rew"] = np.concatenate([np.asarray(ro.rewards, dtype=np.float64) for ro in ros])
+        out[f"dvs_{tag}_torch"] = discounted_values(ros, 0.97, "torch").numpy().astype(np.float64)
+        if tag == "eq":
+            out[f"dvs_{tag}_numpy"] = np.asarray(discounted_values(ros, 0.97, "numpy"), dtype=np.float64)
+        print(f"  discounted_values {tag}: torch shape {out[f'dvs_{tag}_torch'].shape}")
     np.savez_compressed(osp.join(OUT, "returns_reference.npz"), **out)
 
 

@@ -23,6 +23,7 @@ REW_QUADR, REW_EXP, REW_SCALED_EXP = 0, 1, 2
 FR_ENABLED, FR_STATE_DEP, FR_TIME_DEP, FR_ALWAYS_POS, FR_ALWAYS_NEG = 1, 2, 4, 8, 16
 POL_ACTIONS, POL_FNN, POL_LINEAR, POL_IDLE = 0, 1, 2, 3
 PREC_FP32, PREC_TF32X3, PREC_TF32 = 0, 1, 2
+STEP_YIELDED_FINAL, STEP_COUNT_MASK = 1 << 30, 0x3FFFFFFF
 ACT_NOISE_NONE, ACT_NOISE_NORMAL, ACT_NOISE_UNIFORM = 0, 1, 2
 ENV_ACT_NOISE_NONE, ENV_ACT_NOISE_OUTER, ENV_ACT_NOISE_INNER = 0, 1, 2
 FEATS = dict(const=0, identity=1, sign=2, abs=3, squared=4, cubic=5, sin=6, cos=7, sinsin=8, sincos=9)

@@ -101,12 +101,15 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     for (int i = 0; i < E::DP; i++) dp[i] = params ? params[n * E::DP + i] : cfg.base_params[i];
     Lane<KIND, R> L;
     L.set_params(cfg, dp);
-    L.yielded_final = 0;
 #pragma unroll
     for (int i = 0; i < E::DS; i++) L.s[i] = state[n * E::DS + i];
 #pragma unroll
     for (int i = 0; i < E::NH; i++) L.h[i] = hidden[n * NHS + i];
-    L.curr_step = curr_step[n];
+    // FinalRewTask yields its final reward ONCE per episode (tasks/final_reward.py:131-135): the flag travels between
+    // step launches in bit 30 of the step counter (SRE_STEP_YIELDED_FINAL), cleared by sre_reset
+    const int cs = curr_step[n];
+    L.curr_step = cs & SRE_STEP_COUNT_MASK;
+    L.yielded_final = (cs & SRE_STEP_YIELDED_FINAL) ? 1 : 0;
     R a[E::DA];
     int st = 0;
 #pragma unroll
@@ -131,7 +134,7 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     for (int i = 0; i < E::DS; i++) state[n * E::DS + i] = L.s[i];
 #pragma unroll
     for (int i = 0; i < E::NH; i++) hidden[n * NHS + i] = L.h[i];
-    curr_step[n] = L.curr_step;
+    curr_step[n] = L.curr_step | (L.yielded_final ? SRE_STEP_YIELDED_FINAL : 0);
     L.observe(o);
     if (cfg.obs_noise)
         add_obs_noise<E::DO, R>(cfg, seed, env_offset + (unsigned long long)n, episode, (uint32_t)L.curr_step, o);

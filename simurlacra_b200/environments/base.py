@@ -15,16 +15,20 @@ class Env(ABC):
     name: str = None  # unique identifier
 
     def __init__(self, dt: Union[int, float], max_steps: Union[int, float] = pyrado.inf):
-        if not isinstance(dt, (int, float)):
-            raise pyrado.TypeErr(given=dt, expected_type=(int, float))
+        """Same argument contract as the reference (environments/base.py:55-60): a non-number `dt` is a TypeErr, a
+        negative `dt` or `max_steps < 1` a ValueErr."""
+        self._check_number(dt)
         if dt < 0:
             raise pyrado.ValueErr(given=dt, ge_constraint="0")
         if max_steps < 1:
             raise pyrado.ValueErr(given=max_steps, ge_constraint="1")
-        self._dt = float(dt)
-        self._max_steps = max_steps
-        self._curr_step = 0
-        self._curr_rew = -pyrado.inf
+        self._dt, self._max_steps = float(dt), max_steps
+        self._curr_step, self._curr_rew = 0, -pyrado.inf
+
+    @staticmethod
+    def _check_number(x):
+        if not isinstance(x, (int, float)):
+            raise pyrado.TypeErr(given=x, expected_type=(int, float))
 
     @property
     @abstractmethod
@@ -51,9 +55,8 @@ class Env(ABC):
 
     @dt.setter
     def dt(self, dt: Union[int, float]):
-        if not isinstance(dt, (float, int)):
-            raise pyrado.TypeErr(given=dt, expected_type=[float, int])
-        if not dt > 0:
+        self._check_number(dt)
+        if dt <= 0:
             raise pyrado.ValueErr(given=dt, g_constraint="0")
         self._dt = float(dt)
 
@@ -63,9 +66,10 @@ class Env(ABC):
 
     @max_steps.setter
     def max_steps(self, num_steps: Union[int, float]):
-        if not (isinstance(num_steps, int) or num_steps == pyrado.inf):
-            raise pyrado.TypeErr(msg=f"Number of steps needs to be an integer of infinite, but is {num_steps}")
-        if not num_steps > 0:
+        unbounded = num_steps == pyrado.inf
+        if not (unbounded or isinstance(num_steps, int)):
+            raise pyrado.TypeErr(msg=f"max_steps takes an int or pyrado.inf, got {num_steps!r}")
+        if num_steps <= 0:
             raise pyrado.ValueErr(given=num_steps, g_constraint="0")
         self._max_steps = num_steps
 

@@ -252,7 +252,7 @@ class SimPyEnv(SimEnv):
     def curr_step(self):
         if self._curr_step_t is None or self.num_envs == 1:
             return self._curr_step
-        return self._curr_step_t
+        return self._curr_step_t & L.STEP_COUNT_MASK  # bit 30 carries the FinalRewTask "yielded" flag (include/sre.h)
 
     def observe(self, state) -> np.ndarray:
         """Noise-free observation of a given state (Env.observe, environments/base.py:203 and the overrides)."""

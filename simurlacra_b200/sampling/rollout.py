@@ -162,6 +162,13 @@ def _fused_rollout(env, cc: CompiledChain, desc, max_steps, reset_kwargs, stop_o
     return sequences_from_records(env, sim, res, sim.dt, data_format)
 
 
+def _state_copy(env):
+    """rollout.py:237 `env.state.copy()`: a bare batched SimPyEnv hands out its LIVE device tensor, which the step
+    kernel overwrites in place -- without the copy every recorded state would alias the final one."""
+    s = env.state
+    return s.clone() if isinstance(s, torch.Tensor) else np.array(s, copy=True)
+
+
 def _hidden_of(sim):
     if isinstance(sim, SimPyEnv) and sim._dims["nh"] > 0 and sim.hidden_state is not None:
         return sim.hidden_state.clone()
@@ -199,7 +206,7 @@ def _generic_rollout(env, policy, eval, reset_kwargs, no_reset, stop_on_done, re
             raise pyrado.ValueErr(msg="At least one action value is NaN!")
         act = act_to.detach().to(sim.device) if batch else act_to.detach().cpu().numpy()
         t1 = time.time()
-        state = env.state
+        state = _state_copy(env)
         hid = _hidden_of(sim)
         obs_next, rew, done, _ = env.step(act)
         act_app = env.limit_act(act)
@@ -211,7 +218,7 @@ def _generic_rollout(env, policy, eval, reset_kwargs, no_reset, stop_on_done, re
         steps += 1
         finished = (finished | done) if batch and stop_on_done else (done if not batch else finished)
     hist["obs"].append(obs)
-    hist["state"].append(env.state)
+    hist["state"].append(_state_copy(env))
     hist["hidden"].append(_hidden_of(sim))
     if steps == 0:
         raise pyrado.ShapeErr(msg="StepSequence must not be empty!")

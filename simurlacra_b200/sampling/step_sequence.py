@@ -394,12 +394,20 @@ def discounted_value(rollout: StepSequence, gamma: float):
 
 
 def discounted_values(rollouts: Sequence[StepSequence], gamma: float, data_format: Optional[str] = "torch"):
-    """Discounted returns-to-go of several rollouts, concatenated as a column vector (:1075-1090)."""
+    """Discounted returns-to-go of several rollouts with the reference's return shapes (:1075-1090): 'torch' gives ONE
+    1-D tensor (the rollouts concatenated), 'numpy' gives `np.array([...])` with one row per rollout ([n_ro, len] for
+    equally long rollouts)."""
     if data_format == "torch":
-        return torch.cat([torch.as_tensor(discounted_value(ro, gamma)).to(torch.get_default_dtype()).view(-1, 1)
+        return torch.cat([torch.as_tensor(discounted_value(ro, gamma)).to(torch.get_default_dtype()).reshape(-1)
                           for ro in rollouts])
     if data_format == "numpy":
-        return np.concatenate([np.asarray(discounted_value(ro, gamma)).reshape(-1, 1) for ro in rollouts])
+        vals = [np.asarray(_to_format(discounted_value(ro, gamma), "numpy"), dtype=np.float64).reshape(-1) for ro in rollouts]
+        if len({len(v) for v in vals}) > 1:  # ragged: numpy >= 1.24 needs the object dtype spelt out
+            out = np.empty(len(vals), dtype=object)
+            for i, v in enumerate(vals):
+                out[i] = v
+            return out
+        return np.array(vals)
     raise pyrado.ValueErr(given=data_format, eq_constraint="'torch' or 'numpy'")
 
 

@@ -77,7 +77,7 @@ def test_single_step_fp64_matches_reference(E, fname, kind_name, kw):
         if d["nh"]:
             np.testing.assert_allclose(hidden[:, : d["nh"]].cpu().numpy(), Hd[1: T + 1], rtol=1e-9, atol=1e-10)
         assert int(status.abs().sum()) == 0
-        assert curr.cpu().numpy().tolist() == list(range(1, T + 1))
+        assert (curr.cpu().numpy() & 0x3FFFFFFF).tolist() == list(range(1, T + 1))  # bit 30: final reward yielded
 
 
 def _rollout_case(E, g, c, kind_name, kw, dtype):
@@ -187,3 +187,43 @@ def test_fp64_sensitivity_of_the_golden_cases(E, fname, kind_name, kw):
         if well.any():
             assert e32[well].max() < 1e-4, (fname, c, e32[well].max())
     assert amp_max > 1e3, (fname, amp_max)
+
+
+@pytest.mark.parametrize("fname,kind_name,kw", [("traj_omo", "omo", {}), ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st"))])
+def test_final_reward_is_yielded_once_when_stepping_past_done(E, orc, fname, kind_name, kw):
+    """FinalRewTask adds its final reward ONCE per episode (tasks/final_reward.py:131-135), also when the caller keeps
+    stepping after `done` (rollout(stop_on_done=False), manual stepping): the step kernel carries the flag between
+    launches.  Checked against the oracle's env object stepped past done with the same actions."""
+    from conftest import OMO_TASK, STAB_TASKS
+    from test_oracle_golden import _make
+
+    g = golden(fname)
+    c = 2
+    kind = E.KIND_BY_NAME[kind_name]
+    d = E.dims(kind)
+    cfg = _cfg(E, kind_name, float(g["dt"]), 0, kw, torch.float64)  # max_steps = inf: only failures end the episode
+    e = _make(orc, kind_name, float(g["dt"]), 0, kw)
+    e.set_params(g[f"c{c}_params"])
+    A = g[f"c{c}_actions"]
+    extra = 30
+    acts = np.concatenate([A, np.tile(A[-1:], (extra, 1))])
+    e.reset(g[f"c{c}_init"])
+    params = _t(g[f"c{c}_params"][None, :], torch.float64)
+    state = torch.empty(1, d["ds"], dtype=torch.float64, device=DEV)
+    hidden = torch.zeros(1, max(d["nh"], 1), dtype=torch.float64, device=DEV)
+    curr = torch.zeros(1, dtype=torch.int32, device=DEV)
+    obs = torch.empty(1, d["do"], dtype=torch.float64, device=DEV)
+    rew = torch.empty(1, dtype=torch.float64, device=DEV)
+    done = torch.empty(1, dtype=torch.uint8, device=DEV)
+    E.reset(cfg, params, _t(g[f"c{c}_init"][None, :], torch.float64), state, hidden, curr, obs)
+    n_done, big = 0, 0
+    for t in range(len(acts)):
+        _, r_ref, d_ref = e.step(acts[t].copy())
+        E.step(cfg, params, _t(acts[t][None, :], torch.float64), state, hidden, curr, obs, rew, done)
+        assert bool(done[0]) == bool(d_ref), t
+        assert abs(float(rew[0]) - r_ref) <= 1e-9 * max(1.0, abs(r_ref)), (t, float(rew[0]), r_ref)
+        n_done += int(d_ref)
+        big += int(abs(r_ref) > 100)
+        if not np.all(np.isfinite(e.state)):
+            break
+    assert n_done >= 2  # the episode was really stepped past its end

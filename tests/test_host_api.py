@@ -14,7 +14,7 @@ import pytest
 import torch
 
 import simurlacra_b200 as pyrado
-from conftest import ROOT
+from conftest import ROOT, golden
 from simurlacra_b200 import _lib as L
 from simurlacra_b200.domain_randomization import (BernoulliDomainParam, DomainRandomizer, NormalDomainParam,
                                                    UniformDomainParam)
@@ -523,3 +523,26 @@ def test_discrete_space_and_ball_on_beam_disc():
     assert env._make_cfg().flags & L.F_DISC_ACT
     env.domain_param = dict(beam_length=1.0)
     np.testing.assert_allclose(env.act_space.eles.reshape(-1), [-14.715, 0.0, 14.715])
+
+
+def test_discounted_values_return_shapes_match_reference():
+    """discounted_values (sampling/step_sequence.py:1075-1090 of the reference): 'torch' -> one 1-D tensor over all
+    rollouts, 'numpy' -> one row per rollout; values generated by the unmodified reference (oracle/gen_golden.py)."""
+    from simurlacra_b200.sampling.step_sequence import StepSequence, discounted_values
+
+    g = golden("returns_reference")
+    for tag in ("eq", "ragged"):
+        lens = [int(x) for x in g[f"dvs_{tag}_lens"]]
+        rew = g[f"dvs_{tag}_rew"]
+        ros, o = [], 0
+        for n in lens:
+            ros.append(StepSequence(rewards=rew[o:o + n], observations=np.zeros((n + 1, 2)), actions=np.zeros((n, 1)), complete=True))
+            o += n
+        t = discounted_values(ros, 0.97, "torch")
+        assert isinstance(t, torch.Tensor) and t.dim() == 1 and t.shape[0] == sum(lens)
+        np.testing.assert_allclose(t.double().numpy(), g[f"dvs_{tag}_torch"], rtol=1e-6, atol=1e-6)
+        a = discounted_values(ros, 0.97, "numpy")
+        assert len(a) == len(lens)
+        if tag == "eq":
+            assert a.shape == g["dvs_eq_numpy"].shape
+            np.testing.assert_allclose(a, g["dvs_eq_numpy"], rtol=1e-12)
