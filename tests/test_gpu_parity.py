@@ -119,15 +119,16 @@ def test_trajectory_fp64_matches_reference(E, fname, kind_name, kw):
         assert int(res["status"][0]) == 0
 
 
-# fp32 over the full horizon: 1e-4 for the non-chaotic envs; the swing-up pendulums are chaotic under the large
-# injected actions of the golden cases, so they are checked over the first 100 steps only
-FP32_TOL = {"traj_omo": (1e-4, None), "traj_bob": (1e-4, None), "traj_qbb": (1e-4, None), "traj_qbb_simple": (1e-4, None),
-            "traj_qq-su": (2e-4, 100), "traj_qcp-su": (2e-4, 100), "traj_qcp-su_simple": (2e-4, 100),
-            "traj_pend": (1e-4, None), "traj_qq-st": (2e-4, 100), "traj_qcp-st": (2e-4, 50), "traj_qcp-st_simple": (2e-4, 50),
-            "traj_bob-d": (1e-4, None),
-            # the swing-up pendulums in their non-chaotic regime: north_star's bar over the FULL horizon
-            "traj_qq-su_calm": (1e-4, None), "traj_qcp-su_calm": (1e-4, None), "traj_qcp-su_calm_simple": (1e-4, None)}
-EXACT_LENGTH_FP32 = ("traj_qq-su_calm", "traj_qcp-su_calm", "traj_qcp-su_calm_simple")
+# fp32 (production build) against the reference's fp64 trajectories: north_star's bar -- 1e-4 over the FULL horizon,
+# episode lengths bit-exact -- on every golden file but one.  Round 1 compared the swing-up cases over their first 100
+# steps only, calling them chaotic; test_fp64_sensitivity_of_the_golden_cases measured it: a 1e-9 perturbation grows by
+# at most 35x (qq-su), 44x (qcp-su), 60x (qcp-su simple), 136x (qcp-st) over the horizon, and the float32 build stays
+# within 6e-5 everywhere.  The exception is QQubeStabSim (unstable upright equilibrium, amplification up to 1e3,
+# float32 error 3e-4 at 600 steps): 1e-4 is asserted there on the well-conditioned window by the sensitivity test.
+FP32_TOL = {f: (1e-4, None) for f, _, _ in ENV_FILES}
+FP32_TOL["traj_qq-st"] = (1e-3, None)
+SENSITIVITY_FILES = ("traj_qq-su", "traj_qcp-su", "traj_qcp-su_simple", "traj_qq-st", "traj_qcp-st", "traj_qcp-st_simple")
+EXACT_LENGTH_FP32 = tuple(f for f, _, _ in ENV_FILES)
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", ENV_FILES)
@@ -141,10 +142,7 @@ def test_trajectory_fp32(E, fname, kind_name, kw):
         Tn = int(g[f"c{c}_length"])
         n = min(Tn, upto) if upto else Tn
         Tl = int(res["length"][0])
-        if fname in EXACT_LENGTH_FP32:
-            assert Tl == Tn, (fname, c, Tl, Tn)  # episode lengths bit-exact (north_star)
-        elif upto is None:
-            assert abs(Tl - Tn) <= 1  # a bound crossing may move by one step in fp32
+        assert Tl == Tn, (fname, c, Tl, Tn)  # episode lengths bit-exact (north_star)
         m = min(n, Tl)
         st = res["state"][: m + 1, 0].double().cpu().numpy()
         err = np.abs(st - S[: m + 1]) / np.maximum(1.0, np.abs(S[: m + 1]))
@@ -152,16 +150,15 @@ def test_trajectory_fp32(E, fname, kind_name, kw):
     assert worst < tol, (fname, worst)
 
 
-@pytest.mark.parametrize("fname,kind_name,kw", [e for e in ENV_FILES if FP32_TOL[e[0]][1] is not None])
+@pytest.mark.parametrize("fname,kind_name,kw", [e for e in ENV_FILES if e[0] in SENSITIVITY_FILES])
 def test_fp64_sensitivity_of_the_golden_cases(E, fname, kind_name, kw):
-    """Why the large-action swing-up / stabilisation cases are compared over their first 50-100 steps only in float32:
-    the fp64 build's OWN sensitivity.  Every case is run twice in fp64, the second time with the initial state moved by
-    1e-9 (relative to the state scale); g(t) = |delta s(t)| / 1e-9 is the amplification of a perturbation.  A float32
-    trajectory carries a per-step rounding error of ~6e-8 of the state scale, so its distance to the fp64 reference is
-    bounded by ~6e-8 * sum_t g -- the test asserts (a) that the float32 build stays within 1e-4 wherever that bound is
-    below 1e-4 (i.e. the float32 error is explained by conditioning, not by the kernel), and (b) that the cases really
-    are ill-conditioned beyond the compared window (amplification > 1e3 somewhere), which is why 1e-4 over the full
-    horizon is asserted on the `_calm` cases instead."""
+    """Conditioning of the large-action swing-up / stabilisation golden cases, measured on the fp64 build itself: every
+    case is run twice in fp64, the second time with the initial state moved by 1e-9 (relative to the state scale);
+    g(t) = |delta s(t)| / 1e-9 is the amplification of a perturbation.  A float32 trajectory carries a per-step rounding
+    error of ~6e-8 of the state scale, so its distance to the fp64 reference is bounded by ~6e-8 * sum_t g(t): the test
+    asserts that the float32 build stays within 1e-4 wherever that bound is below 1e-4 (the float32 error is explained
+    by conditioning, not by the kernel) and prints the amplification, which is what justifies the one relaxed entry
+    of FP32_TOL (QQubeStabSim)."""
     g = golden(fname)
     amp_max = 0.0
     for c in range(int(g["n_cases"])):
@@ -186,7 +183,7 @@ def test_fp64_sensitivity_of_the_golden_cases(E, fname, kind_name, kw):
               f"{int(well.sum())}/{m32 + 1}, fp32 err there {e32[well].max() if well.any() else 0:.2e}, overall {e32.max():.2e}")
         if well.any():
             assert e32[well].max() < 1e-4, (fname, c, e32[well].max())
-    assert amp_max > 1e3, (fname, amp_max)
+    print(f"{fname}: max amplification over all cases {amp_max:.3g}")
 
 
 @pytest.mark.parametrize("fname,kind_name,kw", [("traj_omo", "omo", {}), ("traj_qcp-st", "qcp-su", dict(long_pole=True, stab="qcp-st"))])
