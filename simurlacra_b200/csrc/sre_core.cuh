@@ -12,6 +12,7 @@ template <typename R> struct KTask {
     R Q[SRE_MAX_DS * SRE_MAX_DS];
     R Rm[SRE_MAX_DA * SRE_MAX_DA];
     R radial_mod[SRE_MAX_DS];
+    R radial_inv[SRE_MAX_DS];  // 1 / radial_mod (host-computed, for m_fmod_pos)
     R final_factor;
     double min_rew;
     int rew_kind;
@@ -43,7 +44,8 @@ struct KDistr {
 // selected indices, then the +-pi wrap on EVERY element), reward functions tasks/reward_functions.py:202-222
 // (Quadr), :237-244 (ExpQuadr), :276-282 (ScaledExpQuadr).  act is the UNCLIPPED action (base.py:220).
 // ------------------------------------------------------------------------------------------------------
-template <int DS, int DA, typename R>
+// PLAIN (compile time): diagonal Q / R known to the caller -- the dense branch is not compiled in.
+template <int DS, int DA, typename R, bool PLAIN = false>
 SRE_DEV R step_rew(const KTask<R> &tk, const R *state, const R *act, R c_max) {
     R err[DS];
 #pragma unroll
@@ -52,7 +54,7 @@ SRE_DEV R step_rew(const KTask<R> &tk, const R *state, const R *act, R c_max) {
         const R pi = (R)SRE_PI, two_pi = (R)(2 * SRE_PI);
 #pragma unroll
         for (int i = 0; i < DS; i++)
-            if (tk.radial_mask & (1u << i)) err[i] = m_fmod(err[i], tk.radial_mod[i]);
+            if (tk.radial_mask & (1u << i)) err[i] = m_fmod_pos(err[i], tk.radial_mod[i], tk.radial_inv[i]);
 #pragma unroll
         for (int i = 0; i < DS; i++) {
             if (err[i] > pi) err[i] = two_pi - err[i];
@@ -60,7 +62,7 @@ SRE_DEV R step_rew(const KTask<R> &tk, const R *state, const R *act, R c_max) {
         }
     }
     R cost = (R)0;
-    if (tk.q_diag) {
+    if (PLAIN || tk.q_diag) {
 #pragma unroll
         for (int i = 0; i < DS; i++) cost += tk.Q[i * DS + i] * (err[i] * err[i]);
 #pragma unroll
@@ -131,6 +133,41 @@ template <int KIND, typename R> struct Lane {
     // Env.observe (environments/base.py:203 and the overrides); also refreshes `trig`
     SRE_DEV void observe(R *obs) { E::observe(s, obs, trig); }
 
+    // A prepared episode start parked in shared memory (rollout kernel): everything set_params + reset produce, one
+    // column per lane (`p` points at the lane's column, consecutive fields are `stride` reals apart: conflict-free).
+    static constexpr int NC = sizeof(typename E::Consts) / sizeof(R);
+    static constexpr int NHS = E::NH > 0 ? E::NH : 1;
+    static constexpr int NSLOT = NC + 3 * E::DS + 2 * E::DA + 1 + E::NH;
+    SRE_DEV void store_slot(R *p, int stride) const {
+        const R *cc = reinterpret_cast<const R *>(&c);
+        int k = 0;
+#pragma unroll
+        for (int i = 0; i < NC; i++) p[(k++) * stride] = cc[i];
+#pragma unroll
+        for (int i = 0; i < E::DS; i++) { p[(k++) * stride] = st_lo[i]; p[(k++) * stride] = st_up[i]; p[(k++) * stride] = s[i]; }
+#pragma unroll
+        for (int i = 0; i < E::DA; i++) { p[(k++) * stride] = act_lo[i]; p[(k++) * stride] = act_up[i]; }
+        p[(k++) * stride] = c_max;
+#pragma unroll
+        for (int i = 0; i < E::NH; i++) p[(k++) * stride] = h[i];
+    }
+    SRE_DEV void load_slot(const R *p, int stride) {
+        R *cc = reinterpret_cast<R *>(&c);
+        int k = 0;
+#pragma unroll
+        for (int i = 0; i < NC; i++) cc[i] = p[(k++) * stride];
+#pragma unroll
+        for (int i = 0; i < E::DS; i++) { st_lo[i] = p[(k++) * stride]; st_up[i] = p[(k++) * stride]; s[i] = p[(k++) * stride]; }
+#pragma unroll
+        for (int i = 0; i < E::DA; i++) { act_lo[i] = p[(k++) * stride]; act_up[i] = p[(k++) * stride]; }
+        c_max = p[(k++) * stride];
+#pragma unroll
+        for (int i = 0; i < E::NH; i++) h[i] = p[(k++) * stride];
+        if (E::NH == 0) h[0] = (R)0;
+        curr_step = 0;
+        yielded_final = 0;
+    }
+
     // domain_param setter: _calc_constants + _create_spaces + task.reset (base.py:112-124)
     SRE_DEV void set_params(const KCfg<R> &cfg, const R *dp) {
         E::derive(dp, cfg.flags, c, st_lo, st_up, act_lo, act_up);
@@ -199,9 +236,10 @@ template <int KIND, typename R> struct Lane {
 
     // SimPyEnv.step (base.py:217-241).  act: inner-env units, unclipped.  Returns done; *inside gets the
     // contains() code (-1 = NaN state, the reference raises ValueErr at spaces/box.py:142).
-    SRE_DEV bool step(const KCfg<R> &cfg, const R *act, R &rew, int &inside) {
-        const long long remaining = cfg.max_steps > 0 ? cfg.max_steps - (curr_step + 1) : 0;
-        R r = step_rew<E::DS, E::DA, R>(cfg.task, s, act, c_max);
+    // PLAIN (compile time): no FinalRewTask and diagonal Q / R (the caller checked), nothing of either is compiled in
+    template <bool PLAIN = false> SRE_DEV bool step(const KCfg<R> &cfg, const R *act, R &rew, int &inside) {
+        const long long remaining = (!PLAIN && cfg.max_steps > 0) ? cfg.max_steps - (curr_step + 1) : 0;
+        R r = step_rew<E::DS, E::DA, R, PLAIN>(cfg.task, s, act, c_max);
         R a[E::DA];
         limit_act(cfg, act, a);
         E::step(c, cfg.dt, cfg.flags, s, h, a, trig);  // trig belongs to the pre-step state
@@ -210,7 +248,7 @@ template <int KIND, typename R> struct Lane {
         bool done = (inside != 1);  // never_succeeded: done == has_failed (tasks/base.py:159-172)
         const bool failed = done;
         if (cfg.max_steps > 0 && curr_step >= cfg.max_steps) done = true;
-        if (done) r += final_rew(cfg, failed, remaining);
+        if (!PLAIN && done) r += final_rew(cfg, failed, remaining);
         rew = r;
         return done;
     }

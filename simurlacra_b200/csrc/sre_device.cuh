@@ -62,6 +62,23 @@ SRE_DEV float m_sqrt(float x) { return sqrtf(x); }
 SRE_DEV double m_sqrt(double x) { return sqrt(x); }
 SRE_DEV float m_fmod(float x, float y) { return fmodf(x, y); }
 SRE_DEV double m_fmod(double x, double y) { return fmod(x, y); }
+// fmod for quotients of a few units (angle errors against a 2 pi period): q = trunc(x / y) from one multiplication by
+// the host-computed reciprocal, corrected by at most one, then r = x - q y in ONE fma.  The true remainder is exactly
+// representable whenever |r| < |y| (it is a multiple of the smaller ulp and shorter than 24 bits), so the fma returns
+// fmodf's value bit for bit (the sign of a zero result aside) for |x / y| < 2^22 -- at a dozen straight-line
+// instructions instead of fmodf's division loop and its branches.  y > 0.
+SRE_DEV float m_fmod_pos(float x, float y, float inv_y) {
+    float q = truncf(x * inv_y);
+    const float r0 = fmaf(-q, y, x);
+    const bool neg = x < 0.0f;
+    // wrong side of zero: |q| was one too large; not below |y|: one too small (r0 may be rounded there, the test is not)
+    const bool too_big = neg ? (r0 > 0.0f) : (r0 < 0.0f);
+    const bool too_small = neg ? (r0 <= -y) : (r0 >= y);
+    const float one = neg ? -1.0f : 1.0f;
+    q = too_big ? q - one : (too_small ? q + one : q);
+    return fmaf(-q, y, x);
+}
+SRE_DEV double m_fmod_pos(double x, double y, double inv_y) { return fmod(x, y); }
 SRE_DEV float m_abs(float x) { return fabsf(x); }
 SRE_DEV double m_abs(double x) { return fabs(x); }
 SRE_DEV float m_min(float x, float y) { return fminf(x, y); }

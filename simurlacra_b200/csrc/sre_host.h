@@ -61,7 +61,8 @@ template <typename R> inline void make_kcfg(const sre_env_cfg &c, KCfg<R> &k) {
     bool diag = true;
     for (int i = 0; i < ds; i++) {
         k.task.state_des[i] = (R)c.task.state_des[i];
-        k.task.radial_mod[i] = (R)c.task.radial_mod[i];
+        k.task.radial_mod[i] = (R)std::fabs(c.task.radial_mod[i]);  // fmod(x, y) == fmod(x, |y|)
+        k.task.radial_inv[i] = (R)(1.0 / (double)k.task.radial_mod[i]);
         for (int j = 0; j < ds; j++) {
             k.task.Q[i * ds + j] = (R)c.task.Q[i * ds + j];
             if (i != j && c.task.Q[i * ds + j] != 0.0) diag = false;

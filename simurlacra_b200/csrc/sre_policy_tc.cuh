@@ -414,7 +414,27 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
     struct Ctx {
         uint32_t base, tmem, parity;
         const float *gen;
+#ifdef SRE_TC_TRACE
+        uint32_t *trace;  // debug build: per-warp clock stamps of the steps [SRE_TC_TRACE_S0, +8) of the first 592 CTAs
+        uint32_t step;
+#endif
     };
+#ifdef SRE_TC_TRACE
+#ifndef SRE_TC_TRACE_S0
+#define SRE_TC_TRACE_S0 200
+#endif
+    SRE_DEV static void stamp(Ctx &c, int k) {
+        if ((threadIdx.x & 31) == 0 && c.trace && blockIdx.x < 592 && c.step >= SRE_TC_TRACE_S0 && c.step < SRE_TC_TRACE_S0 + 8) {
+            uint32_t v;
+            if (k == 7) asm volatile("mov.u32 %0, %%smid;" : "=r"(v));
+            else v = (uint32_t)clock();
+            c.trace[((blockIdx.x * 8 + (c.step - SRE_TC_TRACE_S0)) * 4 + (threadIdx.x >> 5)) * 8 + k] = v;
+        }
+    }
+#define SRE_STAMP(c, k) stamp(c, k)
+#else
+#define SRE_STAMP(c, k)
+#endif
 
     SRE_DEV static uint32_t tf32_hi(float x) { return __float_as_uint(x) & 0xFFFFE000u; }
     SRE_DEV static uint32_t sw_off(int row, int k, int kb_bytes) {
@@ -516,17 +536,27 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
     // Hand this warp's 32 rows of the A half to the tensor core.  No CTA barrier: every warp bumps an arrival counter
     // and goes on; the warp that arrives LAST (fourth of the group) issues the 12 MMAs of the half and commits them to
     // the half's mbarrier.  Groups cannot interleave: nobody gets past the mbarrier of a half before all four arrived.
-    SRE_DEV static void publish_half(Ctx &c, int half, uint32_t t_d, uint32_t t_ahi, uint32_t t_alo) {
+    // HALF is a compile-time constant: every descriptor is then (CTA-uniform base + constant), which the compiler keeps
+    // in uniform registers.  With a run-time `half` it wrapped each of the 12 MMAs in an ELECT / R2UR.BROADCAST loop
+    // (14 instructions and a branch per MMA): the tile waited ~1 240 cycles from its last arrival to the wake-up, three
+    // times the 389 cycles the 12 MMAs occupy the tensor pipe (tools/tc_trace.py).
+    template <int HALF> SRE_DEV static void publish_half(Ctx &c, uint32_t t_d, uint32_t t_ahi, uint32_t t_alo) {
+        constexpr int half = HALF;
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if ((threadIdx.x & 31) == 0) {
-            uint32_t old;
+        uint32_t old = 0;
+        if ((threadIdx.x & 31) == 0)
             asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;"
                          : "=r"(old)
                          : "r"(c.base + OFF_CNT + half * 4)
                          : "memory");
-            if ((old & 3u) == 3u) {
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if ((old & 3u) == 3u) {  // warp-uniform: this warp arrived last; ONE elected lane issues (elect.sync keeps the
+                                 // branch uniform for the compiler: plain UTCHMMA, no per-instruction election loop)
+            uint32_t elected;
+            asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(elected));
+            if (elected) {
                 tc_fence_after();
                 uint32_t acc = half;
 #pragma unroll
@@ -552,6 +582,8 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
         const uint32_t lane_base = (uint32_t)(r & ~31) << 16;
         const uint32_t t_d = c.tmem, t_ahi = c.tmem + 64, t_alo = c.tmem + 96;
         unsigned long long x2[IN];
+        SRE_STAMP(c, 0);
+        SRE_STAMP(c, 7);
 #pragma unroll
         for (int i = 0; i < IN; i++) x2[i] = pack2(x[i], x[i]);
 #pragma unroll 1
@@ -561,17 +593,23 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
                 unsigned long long a[8];
                 l1_chunk(sm, x2, half * 32 + ch * 16, a);
                 if (half == 1 && ch == 0) {  // the MMAs of half 0 must have consumed the A columns
+                    SRE_STAMP(c, 2);
                     mbar_wait(c.base + OFF_BAR, c.parity);
                     tc_fence_after();
+                    SRE_STAMP(c, 3);
                 }
                 act_store8(a, lane_base + t_ahi + ch * 16, lane_base + t_alo + ch * 16);
                 act_store8(a + 4, lane_base + t_ahi + ch * 16 + 8, lane_base + t_alo + ch * 16 + 8);
             }
-            publish_half(c, half, t_d, t_ahi, t_alo);
+            SRE_STAMP(c, half == 0 ? 1 : 4);
+            if (half == 0) publish_half<0>(c, t_d, t_ahi, t_alo);
+            else publish_half<1>(c, t_d, t_ahi, t_alo);
         }
+        SRE_STAMP(c, 5);
         mbar_wait(c.base + OFF_BAR + 8, c.parity);
         c.parity ^= 1;
         tc_fence_after();
+        SRE_STAMP(c, 6);
         unsigned long long o2[OUT];
 #pragma unroll
         for (int q = 0; q < OUT; q++) o2[q] = pack2(sm[OFF_B3 / 4 + q], 0.0f);
@@ -607,6 +645,9 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
             out[q] = e + od;
         }
         tc_fence_before();  // orders this step's TMEM reads before the arrival that lets the next MMAs overwrite them
+#ifdef SRE_TC_TRACE
+        c.step++;
+#endif
     }
 };
 

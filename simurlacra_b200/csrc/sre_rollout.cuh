@@ -8,6 +8,7 @@
 #include "sre_core.cuh"
 #include "sre_policy.cuh"
 #include "sre_policy_tc.cuh"
+#include <cstdlib>
 
 namespace sre {
 
@@ -39,6 +40,7 @@ struct KIO {
     double *stats;
     int *status;
     int idle_policy;
+    int prep_slots;  // host: shared memory holds one prepared episode start per lane (auto-reset sampling, see the kernel)
 };
 
 template <int KIND, typename R> struct Rec {
@@ -100,13 +102,25 @@ template <int KIND, typename R> SRE_DEV float qbb_plate_ang(R arm_radius, R plat
     else return 0.f;
 }
 
-template <int KIND, typename R, int PV>
+// MODE (compile time) -- what the step body has to be able to do:
+//   SRE_MODE_GENERIC  everything decided at run time (records, observation noise / normalisation, action noises, dense
+//                     Q / R, FinalRewTask): the kernel of round 1
+//   SRE_MODE_PLAIN    no records, no row flags, none of the optional step-path wrappers, diagonal Q / R, no final reward:
+//                     the body of the sampling hot path (returns + lengths + statistics) with none of those branches
+//   SRE_MODE_PLAIN_REC  the same with trajectory records and row flags always on
+// The host picks the mode from the launch arguments (launch_rollout_pv); results are identical by construction.
+#define SRE_MODE_GENERIC 0
+#define SRE_MODE_PLAIN 1
+#define SRE_MODE_PLAIN_REC 2
+
+template <int KIND, typename R, int PV, int MODE = SRE_MODE_GENERIC>
 __global__ void __launch_bounds__((LaunchShape<R, PV>::THREADS), (LaunchShape<R, PV>::MIN_BLOCKS))
 rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDistr distr,
                const __grid_constant__ KPolicy pol, const __grid_constant__ KIO io) {
     using E = Env<KIND, R>;
     using RC = Rec<KIND, R>;
     constexpr int DS = E::DS, DO = E::DO, DA = E::DA, DP = E::DP, NH = E::NH, W = RC::W;
+    constexpr bool PLAIN = MODE != SRE_MODE_GENERIC;
     // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
     using Fast = FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>;
     constexpr bool TC = PV >= SRE_PV_TC;
@@ -116,15 +130,25 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *sm_w = reinterpret_cast<float *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool has_stage = !(PV >= SRE_PV_TC) || (MODE == SRE_MODE_GENERIC ? io.traj != nullptr : MODE == SRE_MODE_PLAIN_REC);
+    const size_t stage_bytes = has_stage ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0;
     R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
+    constexpr int NSLOT = Lane<KIND, R>::NSLOT;
+    // prepared episode starts: [warp][field][lane]
+    R *slot = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float) + stage_bytes) +
+              (size_t)warp * 32 * NSLOT + (threadIdx.x & 31);
+    const size_t slot_bytes = io.prep_slots ? (size_t)(blockDim.x / 32) * 32 * NSLOT * sizeof(R) : 0;
     float *h1s = sm_w + Fast::W_FLOATS + warp * Fast::H1S_FLOATS;  // only meaningful for the tiled FNN variants
 
     // parameter exploration with CTA-aligned groups: this CTA's parameter set is staged like a single set
     const float *w_cta = pol.weights;
     if (pol.cta_groups) w_cta += ((long long)blockIdx.x * blockDim.x / pol.group_size) * pol.n_weights;
     const bool per_lane_w = pol.group_size > 0 && !pol.cta_groups;
-    if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) +
-                              (io.traj ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0), w_cta);  // the tensor-core block sits behind the staging area (pol.smem_floats = 0)
+#ifdef SRE_TC_TRACE
+    tc.trace = reinterpret_cast<uint32_t *>(io.status);
+    tc.step = 0;
+#endif
+    if (TC) Tc::setup(tc, smem_raw + (size_t)pol.smem_floats * sizeof(float) + stage_bytes + slot_bytes, w_cta);  // the tensor-core block sits behind the staging area and the slots (pol.smem_floats = 0)
     else if (PV >= 16) Fast::stage(w_cta, sm_w);
     else if ((PV == SRE_PV_GENERIC || PV == SRE_PV_LINEAR) && !per_lane_w) stage_generic(pol, w_cta, sm_w);
     __syncthreads();
@@ -137,11 +161,11 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     const uint64_t genv = io.env_offset + (uint64_t)n;
     const int n_valid_lanes = (int)min((long long)32, max((long long)0, N - warp_env0));
     const bool vec_ok = ((N * W * (long long)sizeof(R)) % 16 == 0) && ((reinterpret_cast<size_t>(io.traj) % 16) == 0);
-    const bool record = io.traj != nullptr;
+    const bool record = MODE == SRE_MODE_GENERIC ? io.traj != nullptr : MODE == SRE_MODE_PLAIN_REC;
+    const bool want_flag = MODE == SRE_MODE_GENERIC ? io.row_flag != nullptr : MODE == SRE_MODE_PLAIN_REC;
 
     enum { RUN = 0, CLOSING = 1, IDLE = 2 };
     Lane<KIND, R> L;
-    R dp[DP];
     R obs[DO];
 #pragma unroll
     for (int i = 0; i < DO; i++) obs[i] = (R)0;
@@ -164,13 +188,16 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     // case after the synchronous first episode) the other lanes are put to work instead of idling through the
     // divergent path: lane i draws table entry i of the restarting lane (one Philox block + Box-Muller per warp
     // instead of distr.n per lane), and QBB's two inverse-kinematics solves of each restarting lane run on two lanes.
-    auto start_episode = [&](bool mine, unsigned mask) {
+    // `D` is the lane object the start is written to (the live lane, or a temporary that is parked in a slot), `ep_l` this
+    // lane's index of the episode being started, `live`: the start takes effect now (observation, counters, params_out).
+    auto start_episode = [&](Lane<KIND, R> &D, uint32_t ep_l, bool mine, unsigned mask, bool live) {
         const unsigned FULL = 0xffffffffu;
-        if (mine) {
+        // the episode's domain parameters live only inside this call (the lane keeps the derived constants): nothing of
+        // them stays in registers across the hot loop
+        R dp[DP];
 #pragma unroll
-            for (int i = 0; i < DP; i++)
-                dp[i] = io.params ? static_cast<const R *>(io.params)[n * DP + i] : cfg.base_params[i];
-        }
+        for (int i = 0; i < DP; i++)
+            dp[i] = (io.params && mine) ? static_cast<const R *>(io.params)[n * DP + i] : cfg.base_params[i];
         const int k = __popc(mask);
         // DomainRandWrapperLive.reset (environment_wrappers/domain_randomization.py:141-148)
         if (distr.n > 0 && k <= SRE_COOP_MAX_LANES) {
@@ -178,7 +205,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 const int src = __ffs(m) - 1;
                 const uint32_t g_lo = __shfl_sync(FULL, (uint32_t)genv, src);
                 const uint32_t g_hi = __shfl_sync(FULL, (uint32_t)(genv >> 32), src);
-                const uint32_t ep = __shfl_sync(FULL, episode, src);
+                const uint32_t ep = __shfl_sync(FULL, ep_l, src);
                 float v = 0.f;
                 if (lane < distr.n)
                     v = sample_entry(distr.e[lane], io.seed, ((uint64_t)g_hi << 32) | g_lo, ep, (uint32_t)lane);
@@ -193,7 +220,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             }
         } else if (distr.n > 0 && mine) {
             for (int i = 0; i < distr.n; i++) {
-                const float v = sample_entry(distr.e[i], io.seed, genv, episode, (uint32_t)i);
+                const float v = sample_entry(distr.e[i], io.seed, genv, ep_l, (uint32_t)i);
                 const int pi = distr.e[i].param_index;
 #pragma unroll
                 for (int j = 0; j < DP; j++)
@@ -201,8 +228,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             }
         }
         if (mine) {
-            L.set_params(cfg, dp);
-            if (first_episode && io.params_out) {
+            D.set_params(cfg, dp);
+            if (live && first_episode && io.params_out) {
 #pragma unroll
                 for (int i = 0; i < DP; i++) static_cast<R *>(io.params_out)[n * DP + i] = dp[i];
             }
@@ -214,15 +241,15 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 for (int i = 0; i < DS; i++)
                     if (i < n_cols) init[i] = static_cast<const R *>(io.init)[n * n_cols + i];
             } else {
-                sample_init<KIND, R>(cfg, dp, io.seed, genv, episode, init);
+                sample_init<KIND, R>(cfg, dp, io.seed, genv, ep_l, init);
             }
-            L.reset_state(init, n_cols);
+            D.reset_state(init, n_cols);
         }
         if (KIND == SRE_QBB && !(cfg.flags & SRE_F_SIMPLE_DYN)) {
             // quanser_ball_balancer.py:231-245: plate angles from the inverse kinematics, two 100-iteration solves per
             // episode start.  Worker lane w serves the (w / 2)-th restarting lane of the chunk, axis w & 1.
             const R in0 = mine ? dp[4 % DP] : (R)0, in1 = mine ? dp[3 % DP] : (R)0;
-            const R in2 = mine ? L.s[0] + dp[18 % DP] : (R)0, in3 = mine ? L.s[1 % DS] + dp[19 % DP] : (R)0;
+            const R in2 = mine ? D.s[0] + dp[18 % DP] : (R)0, in3 = mine ? D.s[1 % DS] + dp[19 % DP] : (R)0;
             const int my_rank = __popc(mask & ((1u << lane) - 1u));
             for (int base = 0; base < k; base += 16) {
                 const int serve = base + (lane >> 1);
@@ -234,19 +261,36 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 const int w0 = 2 * (my_rank - base);
                 const float a0 = __shfl_sync(FULL, ang, w0 & 31), a1 = __shfl_sync(FULL, ang, (w0 + 1) & 31);
                 if (mine && my_rank >= base && my_rank < base + 16) {
-                    L.h[0] = (R)a0;
-                    L.h[1 % (NH > 0 ? NH : 1)] = (R)a1;
+                    D.h[0] = (R)a0;
+                    D.h[1 % (NH > 0 ? NH : 1)] = (R)a1;
                 }
             }
         } else if (mine) {
-            E::reset_hidden(dp, cfg.flags, L.s, L.h);
+            E::reset_hidden(dp, cfg.flags, D.s, D.h);
         }
-        if (mine) {
-            L.observe(obs);
+        if (mine && live) {
+            D.observe(obs);
             t_ep = 0;
             ret_ep = (R)0;
             failed_ep = false;
         }
+    };
+    // Prepared episode starts (auto-reset sampling).  What an episode start computes depends only on (seed, env, episode):
+    // every PREP_PERIOD rows the warp computes the NEXT start of all lanes whose slot is empty in ONE convergent pass and
+    // parks it in shared memory; a lane that restarts then only loads its slot (a few dozen instructions at one
+    // active lane instead of the whole DR draw + derive + init + kinematics).  Same values, same order of episodes; a
+    // lane that restarts twice within a period takes the direct path.  `ready` is warp-uniform: bit l = slot of lane l
+    // holds the start of episode `episode + 1` of that lane.
+    constexpr int PREP_PERIOD = 16;
+    const bool prep = io.prep_slots && io.auto_reset;
+    unsigned ready = 0u;
+    auto prepare_slots = [&](unsigned need) {
+        Lane<KIND, R> P;
+        const bool mine = (need >> lane) & 1u;
+        start_episode(P, episode + 1u, mine, need, false);
+        if (mine) P.store_slot(slot, 32);
+        ready |= need;
+        __syncwarp();
     };
     // Episode end.  Per lane: the first episode's return / length.  Statistics: WARP-UNIFORM -- the closing lanes' values
     // are gathered with shuffles, every lane forms the same partial sums and lane 0 issues ONE set of shared-memory
@@ -284,7 +328,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
     };
 
-    start_episode(valid, __ballot_sync(0xffffffffu, valid));
+    start_episode(L, episode, valid, __ballot_sync(0xffffffffu, valid), true);
+    if (prep) prepare_slots(__ballot_sync(0xffffffffu, valid));
 
     for (long long row = 0; row < T; row++) {
         R rec[W];
@@ -295,8 +340,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         bool restart = false, closed = false, closed_complete = false;
         const bool stepping = (lane_state == RUN && row < T - 1);
         const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
-        if ((stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
-        if ((stepping || closing) && cfg.obs_norm) apply_obs_norm<DO, R>(cfg, obs);
+        if (!PLAIN && (stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
+        if (!PLAIN && (stepping || closing) && cfg.obs_norm) apply_obs_norm<DO, R>(cfg, obs);
         // ---- policy (float32).  The tiled FNN is warp-cooperative, so it runs outside the per-lane branches ----
         R act[DA];
         if (PV == SRE_PV_ACTIONS) {
@@ -312,7 +357,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             if (TC) {
                 // CTA-cooperative (tcgen05), no CTA barrier inside.  Every 16 rows the CTA agrees on whether any of
                 // its lanes is still running (the exit has to be CTA-uniform: all four warps feed each MMA)
-                if (!record && !io.row_flag && !io.auto_reset && (row & 15) == 0) {
+                if (!record && !want_flag && !io.auto_reset && (row & 15) == 0) {
                     if (!__syncthreads_or(lane_state != IDLE)) break;
                 }
                 Tc::forward(tc, of, af);
@@ -323,7 +368,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, wsrc, of, DO, af, DA);
                 else linear_forward<DO, DA>(pol, wsrc, of, af);
             }
-            if (pol.act_noise && stepping)
+            if (!PLAIN && pol.act_noise && stepping)
                 add_act_noise<DA>(pol.act_noise, pol.noise_scale, pol.noise_mean, io.seed, genv, episode, (uint32_t)t_ep, af);
 #pragma unroll
             for (int i = 0; i < DA; i++) act[i] = (R)af[i];
@@ -334,12 +379,12 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
 #pragma unroll
             for (int i = 0; i < DA; i++) act_env[i] = act[i];
             // GaussianActNoiseWrapper outside / inside ActNormWrapper (the recorded action stays the policy's)
-            if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER)
+            if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
 #pragma unroll
             for (int i = 0; i < DA; i++)
                 if (cfg.act_norm) act_env[i] = L.act_lo[i] + (act_env[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2;
-            if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER)
+            if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
 #pragma unroll
             for (int i = 0; i < DA; i++) {
@@ -362,7 +407,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             // ---- SimPyEnv.step ----
             R rew;
             int inside;
-            const bool done = L.step(cfg, act_env, rew, inside);
+            const bool done = L.template step<PLAIN>(cfg, act_env, rew, inside);
             if (inside < 0) status |= SRE_ST_NAN_STATE;
             L.observe(obs);
             rec[RC::OFF_REW] = rew;
@@ -402,7 +447,18 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                     }
                 }
                 const unsigned rs = __ballot_sync(0xffffffffu, restart);
-                if (rs) start_episode(restart, rs);
+                const unsigned fast = rs & ready;
+                if (fast) {
+                    if ((fast >> lane) & 1u) {
+                        L.load_slot(slot, 32);
+                        L.observe(obs);
+                        t_ep = 0;
+                        ret_ep = (R)0;
+                        failed_ep = false;
+                    }
+                    ready &= ~fast;
+                }
+                if (rs & ~fast) start_episode(L, episode, restart && !((fast >> lane) & 1u), rs & ~fast, true);
             }
         }
 
@@ -415,13 +471,19 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                                   lane);
             __syncwarp();
         }
-        if (io.row_flag && valid) io.row_flag[row * N + n] = flag;
-        if (!TC && !record && !io.row_flag) {
+        if (prep && (row & (PREP_PERIOD - 1)) == PREP_PERIOD - 1 && row < T - 2) {
+            const unsigned need = __ballot_sync(0xffffffffu, lane_state != IDLE) & ~ready;
+            if (need) prepare_slots(need);
+        }
+        if (want_flag && valid) io.row_flag[row * N + n] = flag;
+        if (!TC && !record && !want_flag) {
             // early exit accounting: the warp leaves when every lane is idle
             if (__ballot_sync(0xffffffffu, lane_state != IDLE) == 0u) break;
         }
     }
+#ifndef SRE_TC_TRACE
     if (valid && io.status) io.status[n] = status;
+#endif
     if (TC) Tc::teardown(tc);
 
     // ---- statistics: one atomic set per CTA ----
@@ -441,20 +503,48 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
 template <int KIND, typename R>
 int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const KIO &io, cudaStream_t stream);
 
-template <int KIND, typename R, int PV>
-static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPolicy &pol, const KIO &io,
-                             cudaStream_t stream) {
+template <int KIND, typename R, int PV, int MODE>
+static int launch_rollout_mode(const KCfg<R> &cfg, const KDistr &distr, const KPolicy &pol, const KIO &io_in,
+                               cudaStream_t stream) {
     constexpr int W = Rec<KIND, R>::W;
     const int threads = LaunchShape<R, PV>::THREADS;
-    const long long blocks = (io.n_envs + threads - 1) / threads;
+    const long long blocks = (io_in.n_envs + threads - 1) / threads;
     size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
-    if (PV >= SRE_PV_TC && !io.traj) smem = 0;  // the staging area is only needed when records are written
+    if (PV >= SRE_PV_TC && !io_in.traj) smem = 0;  // the staging area is only needed when records are written
     if (PV >= SRE_PV_TC) smem += FnnTC2<Env<KIND, R>::DO, Env<KIND, R>::DA>::SMEM_BYTES;
-    auto kern = rollout_kernel<KIND, R, PV>;
+    // prepared episode starts: only where they pay (auto-reset sampling with something to compute per episode) and
+    // where the resident CTAs of an SM still fit its shared memory
+    KIO io2 = io_in;
+    const size_t slot_bytes = (size_t)threads * Lane<KIND, R>::NSLOT * sizeof(R);
+    const char *noprep = getenv("SRE_NO_PREP");
+    io2.prep_slots = io_in.auto_reset && !(noprep && noprep[0] == '1') &&
+                     (smem + slot_bytes + 1024) * LaunchShape<R, PV>::MIN_BLOCKS <= 220 * 1024;
+    if (io2.prep_slots) smem += slot_bytes;
+    const KIO &io = io2;
+    auto kern = rollout_kernel<KIND, R, PV, MODE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     kern<<<(unsigned)blocks, threads, smem, stream>>>(cfg, distr, pol, io);
     return (int)cudaGetLastError();
+}
+
+// The plain bodies exist for the production (float) build of the fused-FNN variants -- the sampling hot path; every other
+// combination runs the generic body.
+template <int KIND, typename R, int PV>
+static int launch_rollout_pv(const KCfg<R> &cfg, const KDistr &distr, const KPolicy &pol, const KIO &io,
+                             cudaStream_t stream) {
+    constexpr bool HAS_PLAIN = sizeof(R) == 4 && PV >= 16;
+    const char *force = getenv("SRE_FORCE_GENERIC");  // tests: the plain bodies must reproduce the generic one bit for bit
+    if (force && force[0] == '1') return launch_rollout_mode<KIND, R, PV, SRE_MODE_GENERIC>(cfg, distr, pol, io, stream);
+    if constexpr (HAS_PLAIN) {
+        const bool plain = !cfg.obs_noise && !cfg.obs_norm && !cfg.env_act_noise && !pol.act_noise && cfg.task.q_diag &&
+                           !(cfg.task.final_flags & SRE_FR_ENABLED);
+        if (plain && !io.traj && !io.row_flag)
+            return launch_rollout_mode<KIND, R, PV, SRE_MODE_PLAIN>(cfg, distr, pol, io, stream);
+        if (plain && io.traj && io.row_flag)
+            return launch_rollout_mode<KIND, R, PV, SRE_MODE_PLAIN_REC>(cfg, distr, pol, io, stream);
+    }
+    return launch_rollout_mode<KIND, R, PV, SRE_MODE_GENERIC>(cfg, distr, pol, io, stream);
 }
 
 template <int KIND, typename R>

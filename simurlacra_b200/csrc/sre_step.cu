@@ -190,7 +190,7 @@ __global__ void task_rew_kernel(const __grid_constant__ KTask<R> tk, int ds, int
     if (tk.radial_mask) {
         const R pi = (R)SRE_PI, two_pi = (R)(2 * SRE_PI);
         for (int i = 0; i < ds; i++)
-            if (tk.radial_mask & (1u << i)) err[i] = m_fmod(err[i], tk.radial_mod[i]);
+            if (tk.radial_mask & (1u << i)) err[i] = m_fmod_pos(err[i], tk.radial_mod[i], tk.radial_inv[i]);
         for (int i = 0; i < ds; i++) {
             if (err[i] > pi) err[i] = two_pi - err[i];
             if (err[i] < -pi) err[i] = -two_pi - err[i];
@@ -217,7 +217,8 @@ static int task_rew_t(const sre_task *task, int ds, int da, double c_max, const 
     memset(&k, 0, sizeof k);
     for (int i = 0; i < ds; i++) {
         k.state_des[i] = (R)task->state_des[i];
-        k.radial_mod[i] = (R)task->radial_mod[i];
+        k.radial_mod[i] = (R)std::fabs(task->radial_mod[i]);
+        k.radial_inv[i] = (R)(1.0 / (double)k.radial_mod[i]);
         for (int j = 0; j < ds; j++) k.Q[i * ds + j] = (R)task->Q[i * ds + j];
     }
     for (int i = 0; i < da * da; i++) k.Rm[i] = (R)task->R[i];

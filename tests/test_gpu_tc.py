@@ -213,3 +213,36 @@ def test_rollout_fp32_fnn64_matches_oracle(E, orc, kind_name, dt, H, kw, prec):
         assert worst.max() < 1e-4, (kind_name, prec, worst.max())
     ok = same & (worst < 1e-4)
     np.testing.assert_allclose(res["ret"].double().cpu().numpy()[ok], ref["ret"][ok], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("kind_name,dt,H,kw,hid", [("qq-su", 1 / 250.0, 120, {}, 64), ("qcp-su", 1 / 250.0, 100, dict(long_pole=True), 64),
+                                                   ("qbb", 0.01, 60, {}, 16), ("qq-su", 1 / 250.0, 90, {}, 32)])
+@pytest.mark.parametrize("record", [False, True])
+def test_specialised_bodies_reproduce_the_generic_kernel_bit_for_bit(E, monkeypatch, kind_name, dt, H, kw, hid, record):
+    """The compile-time specialised step bodies (SRE_MODE_PLAIN / SRE_MODE_PLAIN_REC) and the prepared episode starts
+    parked in shared memory are pure re-arrangements: with auto-reset sampling over several episodes per lane they must
+    give the SAME bits as the generic body with direct episode starts (SRE_FORCE_GENERIC / SRE_NO_PREP select those at
+    launch time): records, row flags, first-episode returns / lengths / parameters and the statistics vector."""
+    L = E_L()
+    kind = E.KIND_BY_NAME[kind_name]
+    d = E.dims(kind)
+    sizes = [d["do"], hid, hid, d["da"]]
+    wd = torch.from_numpy(_weights(sizes, seed=5, scale=0.3)).to(DEV)
+    N = 1000
+    cfg = E.make_cfg(kind, dt, H, dtype=torch.float32, act_norm=True, **kw)
+    distr = _qq_distr(E) if kind_name == "qq-su" else None
+    pol = E.make_policy(L.POL_FNN, wd, sizes=sizes)
+    out = {}
+    for tag, env in (("fast", {}), ("generic", dict(SRE_FORCE_GENERIC="1")), ("noprep", dict(SRE_NO_PREP="1")),
+                     ("neither", dict(SRE_FORCE_GENERIC="1", SRE_NO_PREP="1"))):
+        for k in ("SRE_FORCE_GENERIC", "SRE_NO_PREP"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        out[tag] = E.rollout(cfg, pol, N, 4 * H, device=DEV, distr=distr, seed=3, auto_reset=True, record=record)
+        torch.cuda.synchronize()
+    ref = out["neither"]
+    assert float(ref["stats"][L.STAT_EPISODES]) > 2 * N  # several episodes per lane: restarts really happen
+    for tag in ("fast", "generic", "noprep"):
+        for k in ("ret", "length", "params", "stats", "status") + (("traj", "row_flag") if record else ()):
+            assert torch.equal(out[tag][k], ref[k]), (tag, k)
