@@ -66,8 +66,29 @@ SRE_DEV unsigned long long mul2(unsigned long long a, unsigned long long b) {
 #ifndef SRE_TANH_QUAD
 #define SRE_TANH_QUAD 1
 #endif
+#ifndef SRE_TANH_RCP4
+#define SRE_TANH_RCP4 1  // 1: ONE reciprocal for the four tanh (5 MUFU per quad instead of 6, three more multiplications)
+#endif
 SRE_DEV void tanh4_prescaled(unsigned long long &za, unsigned long long &zb) {
-#if SRE_TANH_QUAD && SRE_TANH_SHARED_RCP
+#if SRE_TANH_RCP4 && SRE_TANH_QUAD && SRE_TANH_SHARED_RCP
+    // a_i = 1 + 2^(z_i) with z clamped to 30 (tanh is exactly 1.0f from z = 26 on), so a_0 a_1 a_2 a_3 <= 2^120 is finite:
+    //   P = (a0 b0)(a1 b1),  r = 1 / P,  1/(a0 b0) = r (a1 b1),  1/(a1 b1) = r (a0 b0),  1/a_i = b_i / (a_i b_i), 1/b_i = a_i / (a_i b_i)
+    float a0, a1, b0, b1, ea0, ea1, eb0, eb1, r, p0, p1;
+    unpack2(za, a0, a1);
+    unpack2(zb, b0, b1);
+    a0 = fminf(a0, 30.0f); a1 = fminf(a1, 30.0f); b0 = fminf(b0, 30.0f); b1 = fminf(b1, 30.0f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ea0) : "f"(a0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ea1) : "f"(a1));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(eb0) : "f"(b0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(eb1) : "f"(b1));
+    const unsigned long long one = pack2(1.0f, 1.0f), m2 = pack2(-2.0f, -2.0f);
+    const unsigned long long pa = add2(pack2(ea0, ea1), one), pb = add2(pack2(eb0, eb1), one);
+    unpack2(mul2(pa, pb), p0, p1);  // p_i = a_i b_i
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p0 * p1));
+    const unsigned long long rp = mul2(pack2(r, r), pack2(p1, p0));  // {1 / p0, 1 / p1}
+    za = fma2(mul2(pb, rp), m2, one);
+    zb = fma2(mul2(pa, rp), m2, one);
+#elif SRE_TANH_QUAD && SRE_TANH_SHARED_RCP
     float a0, a1, b0, b1, ea0, ea1, eb0, eb1, r0, r1, p0, p1;
     unpack2(za, a0, a1);
     unpack2(zb, b0, b1);

@@ -22,6 +22,9 @@ namespace sre {
 #ifndef SRE_COOP_MAX_LANES
 #define SRE_COOP_MAX_LANES 5  // up to this many restarting lanes of a warp draw their parameters cooperatively
 #endif
+#ifndef SRE_PREP_PERIOD
+#define SRE_PREP_PERIOD 32  // rows between two convergent refills of the prepared episode starts (power of two)
+#endif
 #define SRE_PV_TC 1000    // [do,64,64,da] tanh, hidden layer on the tensor cores, 3 x TF32 (sre_policy_tc.cuh)
 #define SRE_PV_TC1 1001   // the same, single TF32 pass
 
@@ -281,7 +284,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     // active lane instead of the whole DR draw + derive + init + kinematics).  Same values, same order of episodes; a
     // lane that restarts twice within a period takes the direct path.  `ready` is warp-uniform: bit l = slot of lane l
     // holds the start of episode `episode + 1` of that lane.
-    constexpr int PREP_PERIOD = 16;
+    constexpr int PREP_PERIOD = SRE_PREP_PERIOD;
     const bool prep = io.prep_slots && io.auto_reset;
     unsigned ready = 0u;
     auto prepare_slots = [&](unsigned need) {
