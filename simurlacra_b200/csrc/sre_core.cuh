@@ -121,8 +121,8 @@ SRE_DEV R compute_cmax(const KTask<R> &tk, const R *st_lo, const R *st_up, const
 // ------------------------------------------------------------------------------------------------------
 template <int KIND, typename R> struct Lane {
     using E = Env<KIND, R>;
-    typename E::Consts c;
-    R st_lo[E::DS], st_up[E::DS], act_lo[E::DA], act_up[E::DA];
+    typename E::Consts c;  // the spaces are rebuilt from these on use (E::bounds): most bounds are compile-time constants,
+                           // the few that depend on a domain parameter are members of Consts -- no bound lives in a register
     R c_max;
     R s[E::DS];
     R h[E::NH > 0 ? E::NH : 1];
@@ -137,16 +137,19 @@ template <int KIND, typename R> struct Lane {
     // column per lane (`p` points at the lane's column, consecutive fields are `stride` reals apart: conflict-free).
     static constexpr int NC = sizeof(typename E::Consts) / sizeof(R);
     static constexpr int NHS = E::NH > 0 ? E::NH : 1;
-    static constexpr int NSLOT = NC + 3 * E::DS + 2 * E::DA + 1 + E::NH;
+    static constexpr int NSLOT = NC + E::DS + 1 + E::NH;
+    SRE_DEV void bounds(int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) const { E::bounds(c, flags, st_lo, st_up, act_lo, act_up); }
+    SRE_DEV void act_bounds(int flags, R *act_lo, R *act_up) const {
+        R st_lo[E::DS], st_up[E::DS];
+        E::bounds(c, flags, st_lo, st_up, act_lo, act_up);
+    }
     SRE_DEV void store_slot(R *p, int stride) const {
         const R *cc = reinterpret_cast<const R *>(&c);
         int k = 0;
 #pragma unroll
         for (int i = 0; i < NC; i++) p[(k++) * stride] = cc[i];
 #pragma unroll
-        for (int i = 0; i < E::DS; i++) { p[(k++) * stride] = st_lo[i]; p[(k++) * stride] = st_up[i]; p[(k++) * stride] = s[i]; }
-#pragma unroll
-        for (int i = 0; i < E::DA; i++) { p[(k++) * stride] = act_lo[i]; p[(k++) * stride] = act_up[i]; }
+        for (int i = 0; i < E::DS; i++) p[(k++) * stride] = s[i];
         p[(k++) * stride] = c_max;
 #pragma unroll
         for (int i = 0; i < E::NH; i++) p[(k++) * stride] = h[i];
@@ -157,9 +160,7 @@ template <int KIND, typename R> struct Lane {
 #pragma unroll
         for (int i = 0; i < NC; i++) cc[i] = p[(k++) * stride];
 #pragma unroll
-        for (int i = 0; i < E::DS; i++) { st_lo[i] = p[(k++) * stride]; st_up[i] = p[(k++) * stride]; s[i] = p[(k++) * stride]; }
-#pragma unroll
-        for (int i = 0; i < E::DA; i++) { act_lo[i] = p[(k++) * stride]; act_up[i] = p[(k++) * stride]; }
+        for (int i = 0; i < E::DS; i++) s[i] = p[(k++) * stride];
         c_max = p[(k++) * stride];
 #pragma unroll
         for (int i = 0; i < E::NH; i++) h[i] = p[(k++) * stride];
@@ -170,7 +171,9 @@ template <int KIND, typename R> struct Lane {
 
     // domain_param setter: _calc_constants + _create_spaces + task.reset (base.py:112-124)
     SRE_DEV void set_params(const KCfg<R> &cfg, const R *dp) {
-        E::derive(dp, cfg.flags, c, st_lo, st_up, act_lo, act_up);
+        E::derive(dp, cfg.flags, c);
+        R st_lo[E::DS], st_up[E::DS], act_lo[E::DA], act_up[E::DA];
+        E::bounds(c, cfg.flags, st_lo, st_up, act_lo, act_up);
         c_max = compute_cmax<E::DS, E::DA, R>(cfg.task, st_lo, st_up, act_lo, act_up);
     }
 
@@ -190,7 +193,9 @@ template <int KIND, typename R> struct Lane {
     }
 
     // BoxSpace.contains (spaces/box.py:138-167): inclusive bounds; 1 inside, 0 outside, -1 NaN
-    SRE_DEV int contains() const {
+    SRE_DEV int contains(int flags) const {
+        R st_lo[E::DS], st_up[E::DS], act_lo[E::DA], act_up[E::DA];
+        E::bounds(c, flags, st_lo, st_up, act_lo, act_up);
         bool nan = false, in = true;
 #pragma unroll
         for (int i = 0; i < E::DS; i++) {
@@ -220,6 +225,8 @@ template <int KIND, typename R> struct Lane {
     // BallOnBeamDiscSim keeps an action that np.isclose()s one of its three elements and else takes the closest
     // element, the first one on ties (discrete.py:119-127).
     SRE_DEV void limit_act(const KCfg<R> &cfg, const R *act, R *a) const {
+        R act_lo[E::DA], act_up[E::DA];
+        act_bounds(cfg.flags, act_lo, act_up);
         if (KIND == SRE_BOB && (cfg.flags & SRE_F_DISC_ACT)) {  // the flag exists for the ball-on-beam only
             const R lo = act_lo[0], up = act_up[0], x = act[0], mid = lo + (up - lo) / (R)2;
             const R d0 = m_abs(x - lo), d1 = m_abs(x - mid), d2 = m_abs(x - up);
@@ -244,7 +251,7 @@ template <int KIND, typename R> struct Lane {
         limit_act(cfg, act, a);
         E::step(c, cfg.dt, cfg.flags, s, h, a, trig);  // trig belongs to the pre-step state
         curr_step += 1;
-        inside = contains();
+        inside = contains(cfg.flags);
         bool done = (inside != 1);  // never_succeeded: done == has_failed (tasks/base.py:159-172)
         const bool failed = done;
         if (cfg.max_steps > 0 && curr_step >= cfg.max_steps) done = true;

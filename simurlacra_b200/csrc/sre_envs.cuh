@@ -27,7 +27,7 @@ template <typename R> struct Env<SRE_QQ, R> {
         R Dp;
         R thold_neg, thold_pos;
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], Rm = dp[1], km = dp[2], mr = dp[3], lr = dp[4], Dr = dp[5], mp = dp[6], lp = dp[7];
         const double Jr = mr * lr * lr / 12, Jp = mp * lp * lp / 12;
         const double c1 = 0.25 * mp * lp * lp;
@@ -41,7 +41,9 @@ template <typename R> struct Env<SRE_QQ, R> {
         c.Dp = dp[8];
         c.thold_neg = dp[9];
         c.thold_pos = dp[10];
-        // _create_spaces :167-181
+    }
+    // _create_spaces :167-181: no bound depends on a domain parameter
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
         const double ms[4] = {115.0 / 180 * SRE_PI, 4 * SRE_PI, 20 * SRE_PI, 20 * SRE_PI};
 #pragma unroll
         for (int i = 0; i < 4; i++) { st_lo[i] = (R)(-ms[i]); st_up[i] = (R)ms[i]; }
@@ -107,8 +109,9 @@ template <typename R> struct Env<SRE_QCP, R> {
         R B_eq, B_p, mplg;     // rhs terms
         R mtg, mpl2, mu_c;     // normal force: mtg - mpl2 * (sin*thdd_in + cos*thd^2)
         R thold_neg, thold_pos;
+        R x_max, xd_max;       // the two state bounds that depend on rail_length
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], m_c = dp[1], l_rail = dp[2], eta_m = dp[3], eta_g = dp[4], K_g = dp[5], J_m = dp[6],
                      r_mp = dp[7], R_m = dp[8], k_m = dp[9], B_p = dp[10], B_eq = dp[11], m_p = dp[12], l_p = dp[13],
                      mu_c = dp[14];
@@ -126,10 +129,13 @@ template <typename R> struct Env<SRE_QCP, R> {
         c.mpl2 = (R)(m_p * l_p / 2);
         c.mu_c = (R)mu_c;
         c.thold_neg = dp[15]; c.thold_pos = dp[16];
-        // _create_spaces :541-549, x_buffer = 0.15 (:79)
-        const double up[4] = {l_rail / 2.0 - 0.15, 4 * SRE_PI, l_rail, 20 * SRE_PI};
+        c.x_max = (R)(l_rail / 2.0 - 0.15);  // _create_spaces :541-549, x_buffer = 0.15 (:79)
+        c.xd_max = (R)l_rail;
+    }
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+        st_up[0] = c.x_max; st_up[1] = (R)(4 * SRE_PI); st_up[2] = c.xd_max; st_up[3] = (R)(20 * SRE_PI);
 #pragma unroll
-        for (int i = 0; i < 4; i++) { st_lo[i] = (R)(-up[i]); st_up[i] = (R)up[i]; }
+        for (int i = 0; i < 4; i++) st_lo[i] = -st_up[i];
         if (flags & SRE_F_QCP_STAB) {  // QCartPoleStabSim._create_spaces :473-482, stab_thold = 15 deg (:467)
             const double thold = 15 / 180.0 * SRE_PI;
             st_lo[1] = (R)(SRE_PI - thold); st_up[1] = (R)(SRE_PI + thold);
@@ -223,8 +229,9 @@ template <typename R> struct Env<SRE_QBB, R> {
         R c_kin;
         R kx_damp, kx_J, kx_m, kx_g;  // ball accel terms divided by zeta (kx_g = c_kin m g r^2 / zeta)
         R Vxp, Vxn, Vyp, Vyn, off_x, off_y;
+        R half_plate;  // the state bound that depends on plate_length
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], m_ball = dp[1], r_ball = dp[2], l_plate = dp[3], r_arm = dp[4], K_g = dp[5],
                      eta_g = dp[6], J_l = dp[7], J_m = dp[8], k_m = dp[9], R_m = dp[10], eta_m = dp[11],
                      B_eq = dp[12], c_frict = dp[13];
@@ -244,10 +251,13 @@ template <typename R> struct Env<SRE_QBB, R> {
         c.kx_m = (R)(m_ball * r2 / zeta);
         c.kx_g = (R)(c_kin * m_ball * g * r2 / zeta);
         c.Vxp = dp[14]; c.Vxn = dp[15]; c.Vyp = dp[16]; c.Vyn = dp[17]; c.off_x = dp[18]; c.off_y = dp[19];
-        // _create_spaces :93-117
-        const double ms[8] = {SRE_PI / 4.0, SRE_PI / 4.0, l_plate / 2.0, l_plate / 2.0, 5 * SRE_PI, 5 * SRE_PI, 0.5, 0.5};
+        c.half_plate = (R)(l_plate / 2.0);
+    }
+    // _create_spaces :93-117
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+        const R ms[8] = {(R)(SRE_PI / 4.0), (R)(SRE_PI / 4.0), c.half_plate, c.half_plate, (R)(5 * SRE_PI), (R)(5 * SRE_PI), (R)0.5, (R)0.5};
 #pragma unroll
-        for (int i = 0; i < 8; i++) { st_lo[i] = (R)(-ms[i]); st_up[i] = (R)ms[i]; }
+        for (int i = 0; i < 8; i++) { st_lo[i] = -ms[i]; st_up[i] = ms[i]; }
         act_lo[0] = act_lo[1] = (R)-3; act_up[0] = act_up[1] = (R)3;  // MAX_ACT_QBB
     }
     // _step_dynamics :247-331
@@ -373,8 +383,9 @@ template <typename R> struct Env<SRE_BOB, R> {
     static constexpr int DS = 4, DO = 4, DA = 1, DP = 8, NH = 0, DINIT = 4;
     struct Consts {
         R m_ball, mg, J_beam, k_frict, k_m, k_g, ang_offset;
+        R half_beam, act_max;  // param-dependent bounds
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], m_ball = dp[1], r_ball = dp[2], m_beam = dp[3], l_beam = dp[4], d_beam = dp[5],
                      c_frict = dp[6];
         // _calc_constants :89-98
@@ -388,12 +399,15 @@ template <typename R> struct Env<SRE_BOB, R> {
         c.k_m = (R)(m_ball / zeta_ball);
         c.k_g = (R)(m_ball * g / zeta_ball);
         c.ang_offset = dp[7];
-        // _create_spaces :48-58
-        const double ms[4] = {l_beam / 2.0, SRE_PI / 4.0, 10.0, SRE_PI};
+        c.half_beam = (R)(l_beam / 2.0);
+        c.act_max = (R)(l_beam / 2.0 * g * 3.0);
+    }
+    // _create_spaces :48-58
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+        const R ms[4] = {c.half_beam, (R)(SRE_PI / 4.0), (R)10.0, (R)SRE_PI};
 #pragma unroll
-        for (int i = 0; i < 4; i++) { st_lo[i] = (R)(-ms[i]); st_up[i] = (R)ms[i]; }
-        const double max_act = l_beam / 2.0 * g * 3.0;
-        act_lo[0] = (R)(-max_act); act_up[0] = (R)max_act;
+        for (int i = 0; i < 4; i++) { st_lo[i] = -ms[i]; st_up[i] = ms[i]; }
+        act_lo[0] = -c.act_max; act_up[0] = c.act_max;
     }
     // _step_dynamics :110-130
     SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
@@ -434,15 +448,19 @@ template <typename R> struct Env<SRE_OMO, R> {
     static constexpr int DS = 2, DO = 2, DA = 1, DP = 3, NH = 0, DINIT = 2;
     struct Consts {
         R A10, A11, B1;
+        R act_max;
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double m = dp[0], k = dp[1], d = dp[2];
         const double omega = sqrt(k / m), zeta = d / (2.0 * sqrt(m * k));  // :89-103
         c.A10 = (R)(-(omega * omega));
         c.A11 = (R)(-2.0 * zeta * omega);
         c.B1 = (R)(1.0 / m);
+        c.act_max = (R)k;
+    }
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
         st_lo[0] = (R)-1; st_up[0] = (R)1; st_lo[1] = (R)-10; st_up[1] = (R)10;  // :54-66
-        act_lo[0] = (R)(-k); act_up[0] = (R)k;
+        act_lo[0] = -c.act_max; act_up[0] = c.act_max;
     }
     // _step_dynamics :105-116: forward Euler on s' = A s + B a
     SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {
@@ -468,15 +486,19 @@ template <typename R> struct Env<SRE_PEND, R> {
     static constexpr int DS = 2, DO = 3, DA = 1, DP = 5, NH = 0, DINIT = 2;
     struct Consts {
         R mgl2, d, inv_J;  // m g l / 2, damping, 1 / (m l^2 / 3)
+        R act_max;
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], m = dp[1], l = dp[2];
         c.mgl2 = (R)(m * g * l / 2.0);
         c.d = dp[3];
         c.inv_J = (R)(1.0 / (m * (l * l) / 3.0));
+        c.act_max = dp[4];
+    }
+    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
         st_lo[0] = (R)(-4 * SRE_PI); st_up[0] = (R)(4 * SRE_PI);  // :66-74
         st_lo[1] = (R)(-4 * SRE_PI); st_up[1] = (R)(4 * SRE_PI);
-        act_lo[0] = -dp[4]; act_up[0] = dp[4];
+        act_lo[0] = -c.act_max; act_up[0] = c.act_max;
     }
     // _step_dynamics :106-122: th_ddot = (tau - m g l / 2 sin th - d thd) / (m l^2 / 3); symplectic Euler
     SRE_DEV static void step(const Consts &c, R dt, int flags, R *s, R *h, R *act, const R *trig) {

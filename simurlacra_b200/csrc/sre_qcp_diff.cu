@@ -165,7 +165,8 @@ SRE_DEV void qcp_load_consts(const KCfg<R> &cfg, const R *params, long long n, t
     R dp[DP];
 #pragma unroll
     for (int i = 0; i < DP; i++) dp[i] = params ? params[n * DP + i] : cfg.base_params[i];
-    Env<SRE_QCP, R>::derive(dp, cfg.flags, c, st_lo, st_up, act_lo, act_up);
+    Env<SRE_QCP, R>::derive(dp, cfg.flags, c);
+    Env<SRE_QCP, R>::bounds(c, cfg.flags, st_lo, st_up, act_lo, act_up);
 }
 
 // forward over the horizon; writes the tape (states, carries) the adjoint reads

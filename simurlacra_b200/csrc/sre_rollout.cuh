@@ -335,14 +335,18 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     if (prep) prepare_slots(__ballot_sync(0xffffffffu, valid));
 
     for (long long row = 0; row < T; row++) {
-        R rec[W];
-#pragma unroll
-        for (int i = 0; i < W; i++) rec[i] = (R)0;
+        // the record of this row goes straight into the warp's staging tile (the pre-step fields before the step: nothing
+        // of a record stays in registers across the dynamics)
+        R *my_rec = stage + lane * W;
         unsigned char flag = SRE_ROW_IDLE;
 
         bool restart = false, closed = false, closed_complete = false;
         const bool stepping = (lane_state == RUN && row < T - 1);
         const bool closing = !stepping && (lane_state == RUN || lane_state == CLOSING);
+        if (record && !stepping) {  // idle rows are all zero, closing rows carry obs / state / hidden only
+#pragma unroll
+            for (int i = 0; i < W; i++) my_rec[i] = (R)0;
+        }
         if (!PLAIN && (stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
         if (!PLAIN && (stepping || closing) && cfg.obs_norm) apply_obs_norm<DO, R>(cfg, obs);
         // ---- policy (float32).  The tiled FNN is warp-cooperative, so it runs outside the per-lane branches ----
@@ -384,36 +388,47 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             // GaussianActNoiseWrapper outside / inside ActNormWrapper (the recorded action stays the policy's)
             if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
+            R a_lo[DA], a_up[DA];
+            L.act_bounds(cfg.flags, a_lo, a_up);
 #pragma unroll
             for (int i = 0; i < DA; i++)
-                if (cfg.act_norm) act_env[i] = L.act_lo[i] + (act_env[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2;
+                if (cfg.act_norm) act_env[i] = a_lo[i] + (act_env[i] + (R)1) * (a_up[i] - a_lo[i]) / (R)2;
             if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
 #pragma unroll
             for (int i = 0; i < DA; i++) {
                 if (m_isnan(act[i])) status |= SRE_ST_NAN_ACT;
                 // rollout.py:244 env.limit_act(act): through ActNormWrapper the NORMALISED action is clipped to [-1, 1]
-                const R lo = cfg.act_norm ? (R)-1 : L.act_lo[i], up = cfg.act_norm ? (R)1 : L.act_up[i];
-                rec[RC::OFF_ACT + i] = act[i];
-                rec[RC::OFF_ACT_APP + i] = m_min(m_max(act[i], lo), up);
+                const R lo = cfg.act_norm ? (R)-1 : a_lo[i], up = cfg.act_norm ? (R)1 : a_up[i];
+                if (record) {
+                    my_rec[RC::OFF_ACT + i] = act[i];
+                    my_rec[RC::OFF_ACT_APP + i] = m_min(m_max(act[i], lo), up);
+                }
             }
-            if (KIND == SRE_BOB && (cfg.flags & SRE_F_DISC_ACT) && !cfg.act_norm) L.limit_act(cfg, act, &rec[RC::OFF_ACT_APP]);
+            if (KIND == SRE_BOB && (cfg.flags & SRE_F_DISC_ACT) && !cfg.act_norm && record) {
+                R app[DA];
+                L.limit_act(cfg, act, app);
+#pragma unroll
+                for (int i = 0; i < DA; i++) my_rec[RC::OFF_ACT_APP + i] = app[i];
+            }
 #pragma unroll
             for (int i = 0; i < DO; i++) {
-                rec[RC::OFF_OBS + i] = obs[i];
+                if (record) my_rec[RC::OFF_OBS + i] = obs[i];
                 if (m_isnan(obs[i])) status |= SRE_ST_NAN_OBS;
             }
+            if (record) {
 #pragma unroll
-            for (int i = 0; i < DS; i++) rec[RC::OFF_STATE + i] = L.s[i];
+                for (int i = 0; i < DS; i++) my_rec[RC::OFF_STATE + i] = L.s[i];
 #pragma unroll
-            for (int i = 0; i < NH; i++) rec[RC::OFF_HIDDEN + i] = L.h[i];
+                for (int i = 0; i < NH; i++) my_rec[RC::OFF_HIDDEN + i] = L.h[i];
+            }
             // ---- SimPyEnv.step ----
             R rew;
             int inside;
             const bool done = L.template step<PLAIN>(cfg, act_env, rew, inside);
             if (inside < 0) status |= SRE_ST_NAN_STATE;
             L.observe(obs);
-            rec[RC::OFF_REW] = rew;
+            if (record) my_rec[RC::OFF_REW] = rew;
             ret_ep += rew;
             t_ep += 1;
             flag = done ? SRE_ROW_DONE : SRE_ROW_STEP;
@@ -423,12 +438,14 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             }
         } else if (closing) {
             // closing row (rollout.py:309-311): final observation / state, nothing else
+            if (record) {
 #pragma unroll
-            for (int i = 0; i < DO; i++) rec[RC::OFF_OBS + i] = obs[i];
+                for (int i = 0; i < DO; i++) my_rec[RC::OFF_OBS + i] = obs[i];
 #pragma unroll
-            for (int i = 0; i < DS; i++) rec[RC::OFF_STATE + i] = L.s[i];
+                for (int i = 0; i < DS; i++) my_rec[RC::OFF_STATE + i] = L.s[i];
 #pragma unroll
-            for (int i = 0; i < NH; i++) rec[RC::OFF_HIDDEN + i] = L.h[i];
+                for (int i = 0; i < NH; i++) my_rec[RC::OFF_HIDDEN + i] = L.h[i];
+            }
             const bool complete = (lane_state == CLOSING);
             flag = complete ? SRE_ROW_TERMINAL : SRE_ROW_TRUNCATED;
             closed = true;
@@ -466,8 +483,6 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
 
         if (record) {
-#pragma unroll
-            for (int i = 0; i < W; i++) stage[lane * W + i] = rec[i];
             __syncwarp();
             if (n_valid_lanes > 0)
                 warp_store_row<R>(stage, static_cast<R *>(io.traj) + (row * N + warp_env0) * W, n_valid_lanes * W, vec_ok,

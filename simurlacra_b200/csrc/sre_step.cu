@@ -18,15 +18,17 @@ __global__ void derive_kernel(const __grid_constant__ KCfg<R> cfg, const R *para
     for (int i = 0; i < E::DP; i++) dp[i] = params ? params[n * E::DP + i] : cfg.base_params[i];
     Lane<KIND, R> L;
     L.set_params(cfg, dp);
+    R slo[E::DS], sup[E::DS], alo[E::DA], aup[E::DA];
+    L.bounds(cfg.flags, slo, sup, alo, aup);
 #pragma unroll
     for (int i = 0; i < E::DS; i++) {
-        if (st_lo) st_lo[n * E::DS + i] = L.st_lo[i];
-        if (st_up) st_up[n * E::DS + i] = L.st_up[i];
+        if (st_lo) st_lo[n * E::DS + i] = slo[i];
+        if (st_up) st_up[n * E::DS + i] = sup[i];
     }
 #pragma unroll
     for (int i = 0; i < E::DA; i++) {
-        if (act_lo) act_lo[n * E::DA + i] = L.act_lo[i];
-        if (act_up) act_up[n * E::DA + i] = L.act_up[i];
+        if (act_lo) act_lo[n * E::DA + i] = alo[i];
+        if (act_up) act_up[n * E::DA + i] = aup[i];
     }
     if (c_max) c_max[n] = L.c_max;
 }
@@ -120,9 +122,11 @@ __global__ void step_kernel(const __grid_constant__ KCfg<R> cfg, const R *params
     }
     const unsigned long long genv = env_offset + (unsigned long long)n;
     if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER) add_env_act_noise<E::DA, R>(cfg, seed, genv, episode, (uint32_t)L.curr_step, a);
+    R a_lo[E::DA], a_up[E::DA];
+    L.act_bounds(cfg.flags, a_lo, a_up);
 #pragma unroll
     for (int i = 0; i < E::DA; i++)
-        if (cfg.act_norm) a[i] = L.act_lo[i] + (a[i] + (R)1) * (L.act_up[i] - L.act_lo[i]) / (R)2;
+        if (cfg.act_norm) a[i] = a_lo[i] + (a[i] + (R)1) * (a_up[i] - a_lo[i]) / (R)2;
     if (cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER) add_env_act_noise<E::DA, R>(cfg, seed, genv, episode, (uint32_t)L.curr_step, a);
     R r;
     int inside;

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--policy", default="bench")
     ap.add_argument("--tag", default="")
     ap.add_argument("--no-dr", action="store_true")
+    ap.add_argument("--wseed", type=int, default=-1)
     a = ap.parse_args()
     import torch
 
@@ -57,7 +58,7 @@ def main():
         if a.hidden == 64:
             hid = 16
     sizes = [n_obs, hid, hid, n_act]
-    w = torch.from_numpy(fnn_weights(sizes, seed=0 if a.policy == "bench" else 3)).to(dev)
+    w = torch.from_numpy(fnn_weights(sizes, seed=a.wseed if a.wseed >= 0 else (0 if a.policy == "bench" else 3))).to(dev)
     if a.policy == "zero":  # zero output layer: the action is 0, nothing fails, episodes run to max_steps (restart-free rate)
         w[-(hid * n_act + n_act):] = 0.0
     if a.no_dr:
