@@ -188,20 +188,25 @@ class ParallelRolloutSampler(SamplerBase):
                     n_keep = max(int(ok[0]) + 1, self.min_rollouts or 0)
             lo, hi = sharding.shard_range(n_keep, rank, ws)
             ros = []
+            st = np.array([0, 0, 0, 0, 0, 0, 1e300, -1e300], dtype=np.float64)
             for start, res in results:
                 ids = np.arange(max(lo, start), min(hi, start + chunk)) - start
                 if len(ids):
                     ros.extend(sequences_from_records(self.env, sim, res, sim.dt, self.data_format, env_ids=ids))
-            for ro in ros:  # statistics of the kept rollouts only
-                r = float(np.sum(ro.rewards)) if self.data_format == "numpy" else float(ro.rewards.sum())
-                stats[L.STAT_EPISODES] += 1
-                stats[L.STAT_SUM_RET] += r
-                stats[L.STAT_SUM_RET2] += r * r
-                stats[L.STAT_SUM_LEN] += ro.length
-                stats[L.STAT_STEPS] += ro.length
-                stats[L.STAT_FAILED] += float(ro.env_done and ro.length < horizon)
-                stats[L.STAT_MIN_RET] = min(float(stats[L.STAT_MIN_RET]), r)
-                stats[L.STAT_MAX_RET] = max(float(stats[L.STAT_MAX_RET]), r)
+                    # statistics of the kept rollouts only, from the kernel's per-lane results (no per-rollout pass)
+                    r = res["ret"].double().cpu().numpy()[ids]
+                    ln = res["length"].cpu().numpy()[ids].astype(np.float64)
+                    flag = res["row_flag"].cpu().numpy()
+                    done = flag[ln.astype(np.int64) - 1, ids] == L.ROW_DONE
+                    st[L.STAT_EPISODES] += len(ids)
+                    st[L.STAT_SUM_RET] += r.sum()
+                    st[L.STAT_SUM_RET2] += (r * r).sum()
+                    st[L.STAT_SUM_LEN] += ln.sum()
+                    st[L.STAT_STEPS] += ln.sum()
+                    st[L.STAT_FAILED] += float((done & (ln < horizon)).sum())
+                    st[L.STAT_MIN_RET] = min(st[L.STAT_MIN_RET], r.min())
+                    st[L.STAT_MAX_RET] = max(st[L.STAT_MAX_RET], r.max())
+            stats = torch.as_tensor(st, device=sim.device)
         self.last_stats = sharding.allreduce_stats(stats) if self._shard is None else stats
         return ros
 

@@ -77,30 +77,102 @@ def _rollout_info(env: Env, sim, params_row: Optional[np.ndarray]) -> dict:
     return info
 
 
+class LazyRolloutInfo(dict):
+    """`rollout_info` of one rollout of a batch: `env_name` / `env_spec` are shared, the `domain_param` dict of the
+    rollout's own (randomized) parameters is built from its row of the kernel's parameter output when it is first asked
+    for -- a sampler call returns tens of thousands of rollouts, most consumers read a handful of these dicts."""
+
+    __slots__ = ("_row", "_names", "_wrappers")
+
+    def __init__(self, base: dict, row, names, wrappers):
+        super().__init__(base)
+        self._row, self._names, self._wrappers = row, names, wrappers
+
+    def _materialise(self):
+        if self._row is not None:
+            dp = {k: float(self._row[i]) for i, k in enumerate(self._names)}
+            for w in self._wrappers:
+                w._set_wrapper_domain_param(dp)
+            self._row = None
+            super().__setitem__("domain_param", dp)
+
+    def __getitem__(self, key):
+        if key == "domain_param":
+            self._materialise()
+        return super().__getitem__(key)
+
+    def get(self, key, default=None):
+        if key == "domain_param":
+            self._materialise()
+        return super().get(key, default)
+
+    def __contains__(self, key):
+        return key == "domain_param" and self._row is not None or super().__contains__(key)
+
+    def keys(self):
+        self._materialise()
+        return super().keys()
+
+    def items(self):
+        self._materialise()
+        return super().items()
+
+    def values(self):
+        self._materialise()
+        return super().values()
+
+    def __iter__(self):
+        self._materialise()
+        return super().__iter__()
+
+    def __len__(self):
+        self._materialise()
+        return super().__len__()
+
+    def __reduce__(self):
+        self._materialise()
+        return (dict, (dict(self),))
+
+
 def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_format: str = "numpy",
                            env_ids: Optional[np.ndarray] = None) -> List[StepSequence]:
-    """Cut the first episode of every lane out of the kernel's time-major record buffer (engine extension)."""
+    """Cut the first episode of every lane out of the kernel's time-major record buffer (engine extension).
+    'torch': every field of every StepSequence is a strided VIEW of the [T, N, W] device buffer (zero copy);
+    'numpy': the used part of the buffer crosses to the host in ONE copy and the fields are views of that array.
+    Per rollout only the container object is created."""
     length = res["length"].cpu().numpy()
-    flags = res["row_flag"]
     n = length.shape[0]
-    t_max = int(length.max()) + 1
-    to_host = (lambda t: t[:t_max].double().cpu().numpy()) if data_format == "numpy" else (lambda t: t[:t_max])
-    obs, act, act_app, rew, state = (to_host(res[k]) for k in ("obs", "act", "act_app", "rew", "state"))
-    hidden = to_host(res["hidden"]) if sim._dims["nh"] > 0 else None
-    done_flag = flags[:t_max].cpu().numpy()
+    ids = np.arange(n) if env_ids is None else np.asarray(env_ids)
+    if len(ids) == 0:
+        return []
+    t_max = int(length[ids].max()) + 1
+    lay, d = E.record_layout(sim.kind), sim._dims
+    if data_format == "numpy":
+        traj = res["traj"][:t_max].cpu().numpy().astype(np.float64, copy=False)  # one D2H copy
+        time_all = np.arange(t_max + 1) * dt
+    else:
+        traj = res["traj"][:t_max]
+        time_all = torch.arange(t_max + 1, dtype=torch.get_default_dtype()) * dt
+    o0, a0, p0, r0, s0, h0 = lay["obs"], lay["act"], lay["act_app"], lay["rew"], lay["state"], lay["hidden"]
+    do, da, ds, nh = d["do"], d["da"], d["ds"], d["nh"]
+    flags_last = res["row_flag"][:t_max].cpu().numpy()
     params = res["params"].double().cpu().numpy()
+    names = sim._param_names if isinstance(sim, SimPyEnv) else ()
+    wrappers = [e for e in all_envs(env) if isinstance(e, EnvWrapper)][::-1]
+    base_info = dict(env_name=env.name, env_spec=env.spec)
+    hname = HIDDEN_FIELD.get(sim.kind, "hidden")
     out = []
-    for i in (range(n) if env_ids is None else env_ids):
+    for i in ids:
         ln = int(length[i])
-        fields = dict(rewards=rew[:ln, i], observations=obs[:ln + 1, i], actions=act[:ln, i],
-                      actions_applied=act_app[:ln, i], states=state[:ln + 1, i])
-        if hidden is not None:
-            h = hidden[:ln + 1, i]
-            fields[HIDDEN_FIELD.get(sim.kind, "hidden")] = h[:, 0] if h.shape[1] == 1 else h
-        done_last = bool(done_flag[ln - 1, i] == L.ROW_DONE)
-        out.append(StepSequence.from_records(fields, ln, dt, rollout_info=_rollout_info(env, sim, params[i]),
-                                             done_last=True, data_format=data_format))
-        out[-1].env_done = done_last  # engine extension: False if the row budget (not the env) ended the episode
+        col = traj[:, i]  # [t_max, W] view
+        fields = dict(rewards=col[:ln, r0], observations=col[:ln + 1, o0:o0 + do], actions=col[:ln, a0:a0 + da],
+                      actions_applied=col[:ln, p0:p0 + da], states=col[:ln + 1, s0:s0 + ds])
+        if nh:
+            fields[hname] = col[:ln + 1, h0] if nh == 1 else col[:ln + 1, h0:h0 + nh]
+        ro = StepSequence.from_views(fields, ln, time_all[:ln + 1], LazyRolloutInfo(base_info, params[i], names, wrappers),
+                                     True, data_format)
+        ro.env_done = bool(flags_last[ln - 1, i] == L.ROW_DONE)  # False if the row budget (not the env) ended the episode
+        out.append(ro)
     return out
 
 

@@ -369,6 +369,27 @@ class StepSequence(Sequence):
                    **{k: v for k, v in fields.items() if k not in ("rewards", "observations", "actions")})
 
 
+def _from_views(cls, fields: dict, length: int, time, rollout_info, done_last: bool, data_format: str) -> "StepSequence":
+    """One complete episode whose fields are already arrays / tensors of the right format and length (views into the
+    kernel's record buffer): no stacking, no validation, no copies -- what `ParallelRolloutSampler.sample()` builds for
+    every rollout index (engine extension; `StepSequence.from_records` is the checked variant)."""
+    self = cls.__new__(cls)
+    self.rollout_info = rollout_info
+    self.continuous = True
+    self._data_format = data_format
+    self._data_names = list(fields.keys()) + ["time"]
+    self.__dict__.update(fields)
+    self.__dict__["time"] = time
+    done = np.zeros(length, dtype=np.bool_)
+    done[-1] = done_last
+    self.done = done
+    self._rollout_bounds = np.array([0, length])
+    return self
+
+
+StepSequence.from_views = classmethod(_from_views)
+
+
 def _info_equal(a, b) -> bool:
     try:
         if isinstance(a, dict) and isinstance(b, dict):
