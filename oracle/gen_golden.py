@@ -531,11 +531,91 @@ def gen_fnn_closed_loop_envs():
     np.savez_compressed(osp.join(OUT, "fnn64_closed_loop_envs.npz"), **out)
 
 
+def gen_diff_extras():
+    """the observation-based differentiable step (`step_diff`, theta rebuilt from
+    (sin, cos)), the straight-through clamp, and the batched differentiable rollout `rollout_tensor_full` with masked
+    resets and per-step Jacobians -- all run on the unmodified reference in float64."""
+    from pyrado.environment_wrappers.action_normalization import dclamp
+    from pyrado.sampling.rollout import rollout_tensor_full
+
+    out = {}
+    dtype = torch.float64
+    torch.set_default_dtype(dtype)
+
+    def mk(max_steps, simple):
+        env = ObsActCatWrapper(ActNormWrapper(QCartPoleSwingUpSim(dt=1 / 20.0, max_steps=max_steps, long=True,
+                                                                  simple_dynamics=simple, wild_init=True)))
+        inner = env._wrapped_env._wrapped_env
+        inner._state_space_bound_lo_tensor = inner._state_space_bound_lo_tensor.to(dtype)
+        inner._state_space_bound_up_tensor = inner._state_space_bound_up_tensor.to(dtype)
+        inner.state_des, inner.Q, inner.R = inner.state_des.to(dtype), inner.Q.to(dtype), inner.R.to(dtype)
+        return env, inner
+
+    # ---- step_diff (observation based), through ActNormWrapper
+    rng = np.random.RandomState(5)
+    for simple in (False, True):
+        env, inner = mk(300, simple)
+        B = 48
+        th = rng.uniform(-np.pi, np.pi, size=B)
+        obs = np.stack([rng.uniform(-0.2, 0.2, B), np.sin(th), np.cos(th), rng.uniform(-0.5, 0.5, B), rng.uniform(-2, 2, B)], 1)
+        act = rng.uniform(-1.2, 1.2, size=(B, 1))
+        thdd = rng.uniform(-1, 1, size=B)
+        o_t = torch.tensor(obs, requires_grad=True)
+        a_t = torch.tensor(act, requires_grad=True)
+        nobs, rew, done, info = env._wrapped_env.step_diff(o_t, a_t, torch.tensor(thdd))
+        wts = torch.tensor(rng.uniform(-1, 1, size=(5,)))
+        loss = (nobs * wts).sum() + rew.sum()
+        g_o, g_a = torch.autograd.grad(loss, [o_t, a_t])
+        key = "sd_simple" if simple else "sd_full"
+        out.update({f"{key}_obs": obs, f"{key}_act": act, f"{key}_thdd": thdd, f"{key}_wts": wts.numpy(),
+                    f"{key}_nobs": nobs.detach().numpy(), f"{key}_rew": rew.detach().numpy(), f"{key}_done": done.numpy(),
+                    f"{key}_thdd_next": info["th_ddot"].detach().numpy(), f"{key}_g_obs": g_o.numpy(), f"{key}_g_act": g_a.numpy()})
+        print(f"  step_diff {key}: |g_obs| {np.abs(g_o.numpy()).max():.4g} done {int(done.sum())}")
+
+    # ---- dclamp: clamp forward, identity backward
+    x = torch.linspace(-2.0, 2.0, 17, requires_grad=True)
+    y = dclamp(x, torch.tensor(-1.0), torch.tensor(1.0))
+    (g,) = torch.autograd.grad((y * torch.arange(17.0)).sum(), [x])
+    out.update(dclamp_x=x.detach().numpy(), dclamp_y=y.detach().numpy(), dclamp_g=g.numpy())
+
+    # ---- rollout_tensor_full(bsz=4): the init states the reference's resets draw are logged in call order
+    env, inner = mk(12, False)
+    W = np.array([[0.8, -0.3, 0.5, 0.2]])
+
+    def policy(obs_to):
+        return torch.tanh(obs_to @ torch.tensor(W).T.to(obs_to))
+
+    inits = []
+    orig_reset = env.reset
+
+    def logging_reset(*a, **k):
+        o = orig_reset(*a, **k)
+        inits.append(np.array(o, dtype=np.float64).copy())
+        return o
+
+    env.reset = logging_reset
+    pyrado.set_seed(3)
+    ros = rollout_tensor_full(env, policy, bsz=4, max_steps=4 * 20)
+    out["rtf_W"], out["rtf_inits"], out["rtf_n"] = W, np.array(inits), np.array(len(ros))
+    out["rtf_max_steps_env"], out["rtf_budget"], out["rtf_bsz"] = np.array(12), np.array(80), np.array(4)
+    for i, ro in enumerate(ros):
+        out[f"rtf{i}_obs"] = np.asarray(ro.observations, dtype=np.float64)
+        out[f"rtf{i}_act"] = np.asarray(ro.actions, dtype=np.float64)
+        out[f"rtf{i}_rew"] = np.asarray(ro.rewards, dtype=np.float64)
+        out[f"rtf{i}_obs_grad"] = np.asarray(ro.env_infos["obs_grad"], dtype=np.float64)
+        out[f"rtf{i}_rew_grad"] = np.asarray(ro.env_infos["rew_grad"], dtype=np.float64)
+        out[f"rtf{i}_th_ddot"] = np.asarray(ro.th_ddot, dtype=np.float64)
+        out[f"rtf{i}_complete"] = np.array(bool(ro.done[-1]))
+    print(f"  rollout_tensor_full: {len(ros)} rollouts, lengths {[len(r) for r in ros]}, {len(inits)} resets")
+    torch.set_default_dtype(torch.float32)
+    np.savez_compressed(osp.join(OUT, "diff_extras.npz"), **out)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
         {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6),
          "wrappers": gen_wrappers, "bob-d": lambda: gen_env_trajs("bob-d", n_cases=6), "calm": gen_calm_trajs,
-         "fnn64": gen_fnn_closed_loop_envs, "dr": gen_dr_moments}[sys.argv[1]]()
+         "fnn64": gen_fnn_closed_loop_envs, "dr": gen_dr_moments, "diff": gen_diff_extras}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)
@@ -557,5 +637,6 @@ if __name__ == "__main__":
     print("wrappers"); gen_wrappers()
     print("calm"); gen_calm_trajs()
     print("fnn64"); gen_fnn_closed_loop_envs()
+    print("diff extras"); gen_diff_extras()
     sz = sum(osp.getsize(osp.join(OUT, f)) for f in os.listdir(OUT))
     print(f"golden size: {sz / 1e6:.2f} MB")

@@ -89,3 +89,12 @@ class ObsActCatWrapper(EnvWrapper):
 
     def step_diff_state(self, obs, act, th_ddot=None):
         return self._wrapped_env.step_diff_state(obs, act, act * 0, th_ddot)
+
+    def step_diff(self, obs, act, th_ddot=None):
+        """:174-179: the last observation column is the previous (normalised) action; the env is stepped with
+        `act + previous action`, and the new "previous action" is that sum through the straight-through clamp."""
+        obs_state = obs[:, :-1]
+        obsn, rew, done, info = self._wrapped_env.step_diff(obs_state, act + obs[:, -1:], th_ddot)
+        act_prev = dclamp(act + obs[:, -1:], torch.tensor(-1.0).to(act), torch.tensor(1.0).to(act))
+        info = dict(info, act_prev=act_prev)
+        return obsn, rew, done, info

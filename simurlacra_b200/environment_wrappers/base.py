@@ -201,6 +201,10 @@ class EnvWrapper(Env):
     def step_diff_state(self, obs, act, act_diff, th_ddot=None):
         return self._wrapped_env.step_diff_state(obs, act, act_diff, th_ddot)
 
+    def step_diff(self, obs, act, th_ddot=None):
+        """Observation-based differentiable step, forwarded down the chain (environment_wrappers/base.py:245-256)."""
+        return self._wrapped_env.step_diff(obs, act, th_ddot)
+
     def render(self, mode: RenderMode = None, render_step: int = 1):
         self._wrapped_env.render(mode, render_step)
 
@@ -249,6 +253,10 @@ class EnvWrapperAct(EnvWrapper):
         if not self._try_fuse(fusion):
             act = self._process_act(act)
         return _call_step(self._wrapped_env, act, fusion)
+
+    def step_diff(self, obs, act, th_ddot=None):
+        """base.py:320-322: the action is processed, the observation passes through."""
+        return self._wrapped_env.step_diff(obs, self._process_act_tensor(act), th_ddot)
 
     def step_diff_state(self, obs, act, act_diff, th_ddot=None):
         """base.py:324-327: both the action and the action offset are processed."""

@@ -86,14 +86,39 @@ class QCartPoleSwingUpSim(SimPyEnv):
         a_un = (act + act_diff).reshape(-1)
         if th_ddot is None:
             th_ddot = torch.zeros(state.shape[0], dtype=state.dtype, device=state.device)
-        cfg = E.make_cfg(self.kind, self._dt, self._max_steps, dtype=state.dtype,
-                         simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init,
-                         task=self._task_struct(), base_params=self.base_param_vector())
-        params = self._params if self._params is not None and self._params.shape[0] == state.shape[0] else None
-        if params is not None and params.dtype != state.dtype:
-            params = params.to(state.dtype)
+        cfg, params = self._diff_cfg(state.dtype), self._diff_params(state.shape[0], state.dtype)
         ns, rew, done, thdd = QcpDiffStep.apply(cfg, params, state, a_un, th_ddot.reshape(-1))
         return ns, rew, done, {"th_ddot": thdd}
+
+    def _diff_cfg(self, dtype):
+        """C-ABI config of the differentiable step in the working dtype of the tensors."""
+        return E.make_cfg(self.kind, self._dt, self._max_steps, dtype=dtype,
+                          simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init,
+                          task=self._task_struct(), base_params=self.base_param_vector())
+
+    def _diff_params(self, n: int, dtype):
+        """Per-env parameter rows if the env holds one row per lane of the batch, else None (the base parameters)."""
+        params = self._params if self._params is not None and self._params.shape[0] == n else None
+        if params is not None and params.dtype != dtype:
+            params = params.to(dtype)
+        return params
+
+    def step_diff(self, obs: torch.Tensor, act: torch.Tensor, th_ddot=None):
+        """The observation-based differentiable step (quanser_cartpole.py:232-254 with `_step_dynamics_diff(state_based=
+        False)`, :332-340): obs [B, 5] = [x, sin th, cos th, x_dot, th_dot]; theta is rebuilt from (sin, cos) with the
+        fork's acos / asin average, the step itself is the RK4 kernel with its adjoint, and the NEXT OBSERVATION comes
+        back.  act [B, 1] in volts (clamped inside; the reward sees the unclamped action)."""
+        x, sin_th, cos_th, x_dot, th_dot = obs[:, 0], obs[:, 1], obs[:, 2], obs[:, 3], obs[:, 4]
+        mask_cos, mask_sin = (cos_th > 0).to(obs.dtype), (sin_th > 0).to(obs.dtype)
+        # the reference builds the masks with `.float()`, so its `np.pi * mask` term is a float32 product whatever the
+        # dtype of the observation (:336-340): pi enters rounded to float32, reproduced here
+        pi32 = float(np.float32(np.pi))
+        th = ((mask_sin * 2 - 1) * torch.acos(cos_th) + (mask_cos * 2 - 1) * torch.asin(sin_th)
+              + pi32 * (2 * mask_sin - 1) * (1 - mask_cos)) / 2
+        state = torch.stack([x, th, x_dot, th_dot], dim=-1)
+        ns, rew, done, info = self.step_diff_state(state, act, None, th_ddot)
+        nobs = torch.stack([ns[:, 0], torch.sin(ns[:, 1]), torch.cos(ns[:, 1]), ns[:, 2], ns[:, 3]], dim=-1)
+        return nobs, rew, done, info
 
     def _task_struct(self):
         t = L.Task()

@@ -271,3 +271,42 @@ class ParallelRolloutSampler(SamplerBase):
                         stop_on_done=True, auto_reset=auto_reset, record=record, traj=traj, row_flag=row_flag)
         self.last_stats = sharding.allreduce_stats(res["stats"]) if self._shard is None else res["stats"]
         return res
+
+
+class ParallelRolloutSamplerTensor(SamplerBase):
+    """The fork's batched sampler for differentiable environments (parallel_rollout_sampler.py:326-500): `sample()` calls
+    `rollout_tensor_full(env, policy, bsz=32, max_steps=min_steps)` until `min_steps` steps (and `min_rollouts` rollouts)
+    have been collected; every StepSequence carries the per-step Jacobians in `env_infos`.  Here the lanes are a batch on
+    the GPU and `bsz` is a constructor argument (the reference hard-codes 32)."""
+
+    def __init__(self, env, policy, num_workers: int = 1, *, min_rollouts: int = None, min_steps: int = None,
+                 show_progress_bar: bool = False, seed: int = NO_SEED, bsz: int = 32):
+        super().__init__(min_rollouts=min_rollouts, min_steps=min_steps)
+        if not isinstance(num_workers, int) or num_workers < 1:
+            raise pyrado.ValueErr(given=num_workers, ge_constraint="1")
+        self.env, self.policy, self.num_workers, self.bsz = env, policy, num_workers, int(bsz)
+        self.show_progress_bar = show_progress_bar
+        self._seed = pyrado.get_base_seed() if seed is NO_SEED else seed
+        self._sample_count = -1
+
+    def reinit(self, env: Optional[Env] = None, policy: Optional[Policy] = None):
+        if env is not None:
+            self.env = env
+        if policy is not None:
+            self.policy = policy
+
+    def sample(self, init_states: Optional[List[np.ndarray]] = None, domain_params: Optional[List[dict]] = None,
+               eval: bool = False) -> List[StepSequence]:
+        from .rollout_tensor import rollout_tensor_full
+
+        self._sample_count += 1
+        if init_states is not None or domain_params is not None or self.min_steps is None:
+            raise NotImplementedError  # like the reference: only the min_steps mode without reset arguments exists
+        result, counter = [], 0
+        while counter < self.min_steps or (self.min_rollouts is not None and len(result) < self.min_rollouts):
+            res = rollout_tensor_full(self.env, self.policy, eval=eval, seed=self._seed if isinstance(self._seed, int) else 0,
+                                      sub_seed=self._sample_count, sub_sub_seed=len(result) + 1, bsz=self.bsz,
+                                      max_steps=self.min_steps)
+            result += res
+            counter += sum(len(r) for r in res)
+        return result

@@ -11,6 +11,7 @@ each `env.step` is a launch of the step kernel, the policy is evaluated as a tor
 
 A batch env (`num_envs > 1`) returns a list with one StepSequence per environment.
 """
+import gc
 import time
 from typing import Callable, List, Optional, Union
 
@@ -162,6 +163,10 @@ def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_f
     base_info = dict(env_name=env.name, env_spec=env.spec)
     hname = HIDDEN_FIELD.get(sim.kind, "hidden")
     out = []
+    # tens of thousands of small containers are created below and none of them is garbage: the cyclic collector would
+    # only rescan them again and again (it took 40 % of this loop)
+    gc_was_on = gc.isenabled()
+    gc.disable()
     for i in ids:
         ln = int(length[i])
         col = traj[:, i]  # [t_max, W] view
@@ -173,6 +178,8 @@ def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_f
                                      True, data_format)
         ro.env_done = bool(flags_last[ln - 1, i] == L.ROW_DONE)  # False if the row budget (not the env) ended the episode
         out.append(ro)
+    if gc_was_on:
+        gc.enable()
     return out
 
 

@@ -103,3 +103,123 @@ def test_adjoint_full_horizon_finite_differences(E):
         ad = g_act[t].cpu().numpy()
         ok = np.abs(fd - ad) <= 1e-4 * np.maximum(1.0, np.abs(ad))
         assert ok.mean() >= 0.8, (t, fd, ad)
+
+
+# ---- observation-based step, straight-through clamp, batched differentiable rollout ----
+def _wgrad_env(max_steps, simple, dtype):
+    from simurlacra_b200.environment_wrappers import ActNormWrapper
+    from simurlacra_b200.environment_wrappers.action_normalization import ObsActCatWrapper
+    from simurlacra_b200.environments.pysim.quanser_cartpole import QCartPoleSwingUpSim
+
+    sim = QCartPoleSwingUpSim(dt=1 / 20.0, max_steps=max_steps, long=True, simple_dynamics=simple, wild_init=True,
+                              device=DEV, dtype=dtype)
+    return ObsActCatWrapper(ActNormWrapper(sim))
+
+
+@pytest.mark.parametrize("simple", [False, True])
+def test_step_diff_obs_based_matches_reference_autograd(simple):
+    """`step_diff` (quanser_cartpole.py:232-254, :332-340): theta rebuilt from (sin, cos), next OBSERVATION returned;
+    values and gradients w.r.t. the observation and the normalised action against the reference's autograd (fp64)."""
+    g = golden("diff_extras")
+    key = "sd_simple" if simple else "sd_full"
+    env = _wgrad_env(300, simple, torch.float64)
+    obs = _t(g[f"{key}_obs"], torch.float64).requires_grad_(True)
+    act = _t(g[f"{key}_act"], torch.float64).requires_grad_(True)
+    nobs, rew, done, info = env.wrapped_env.step_diff(obs, act, _t(g[f"{key}_thdd"], torch.float64))
+    np.testing.assert_allclose(nobs.detach().cpu().numpy(), g[f"{key}_nobs"], rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(rew.detach().cpu().numpy(), g[f"{key}_rew"], rtol=1e-9, atol=1e-11)
+    np.testing.assert_array_equal(done.cpu().numpy().astype(bool), g[f"{key}_done"].astype(bool))
+    np.testing.assert_allclose(info["th_ddot"].detach().cpu().numpy(), g[f"{key}_thdd_next"], rtol=1e-8, atol=1e-9)
+    loss = (nobs * _t(g[f"{key}_wts"], torch.float64)).sum() + rew.sum()
+    g_o, g_a = torch.autograd.grad(loss, [obs, act])
+    np.testing.assert_allclose(g_o.cpu().numpy(), g[f"{key}_g_obs"], rtol=1e-7, atol=1e-8)
+    np.testing.assert_allclose(g_a.cpu().numpy(), g[f"{key}_g_act"], rtol=1e-7, atol=1e-8)
+
+
+def test_dclamp_is_clamp_forward_identity_backward():
+    """DifferentiableClamp / dclamp (action_normalization.py:35-64) against the reference's values and gradient, and
+    inside ObsActCatWrapper.step_diff (the carried previous action)."""
+    from simurlacra_b200.environment_wrappers.action_normalization import dclamp
+
+    g = golden("diff_extras")
+    x = _t(g["dclamp_x"], torch.float64).requires_grad_(True)
+    y = dclamp(x, torch.tensor(-1.0, dtype=torch.float64, device=DEV), torch.tensor(1.0, dtype=torch.float64, device=DEV))
+    np.testing.assert_allclose(y.detach().cpu().numpy(), g["dclamp_y"], rtol=0, atol=0)
+    (gr,) = torch.autograd.grad((y * torch.arange(17.0, dtype=torch.float64, device=DEV)).sum(), [x])
+    np.testing.assert_allclose(gr.cpu().numpy(), g["dclamp_g"], rtol=0, atol=0)  # identity: also outside [-1, 1]
+    # the wrapper's observation-based step: env stepped with act + previous action, previous action through dclamp
+    env = _wgrad_env(300, False, torch.float64)
+    B = 8
+    th = torch.linspace(-2.0, 2.0, B, dtype=torch.float64, device=DEV)
+    prev = torch.linspace(-0.9, 0.9, B, dtype=torch.float64, device=DEV).unsqueeze(1)
+    obs = torch.stack([0.01 * th, torch.sin(th), torch.cos(th), 0.1 * th, 0.3 * th], 1)
+    act = torch.full((B, 1), 0.4, dtype=torch.float64, device=DEV, requires_grad=True)
+    nobs, rew, done, info = env.step_diff(torch.cat([obs, prev], 1), act)
+    ref_nobs, ref_rew, _, _ = env.wrapped_env.step_diff(obs, act.detach() + prev)
+    np.testing.assert_allclose(nobs.detach().cpu().numpy(), ref_nobs.cpu().numpy(), rtol=1e-12)
+    (ga,) = torch.autograd.grad(info["act_prev"].sum(), [act])
+    assert torch.all(ga == 1.0) and float(info["act_prev"].max()) <= 1.0  # 0.4 + 0.9 is clamped, its gradient is not
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-8), (torch.float32, 2e-4)])
+def test_rollout_tensor_full_matches_reference(dtype, tol):
+    """rollout_tensor_full(bsz=4) on ObsActCat(ActNorm(QCartPoleSwingUpSim)) with masked resets against the run of the
+    unmodified reference (same policy, the reference's reset states in call order): number, order, lengths and
+    completeness of the rollouts, observations / actions / rewards / th_ddot and the per-step Jacobians."""
+    from simurlacra_b200.sampling import rollout_tensor_full
+
+    g = golden("diff_extras")
+    env = _wgrad_env(int(g["rtf_max_steps_env"]), False, dtype)
+    W = torch.as_tensor(g["rtf_W"], dtype=dtype)  # the reference run evaluated the policy in float64
+
+    def policy(obs_to):
+        return torch.tanh(obs_to.to(dtype) @ W.T.to(obs_to.device))
+
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(dtype)  # rollout_tensor_full hands the policy observations in the default dtype
+    try:
+        ros = rollout_tensor_full(env, policy, bsz=int(g["rtf_bsz"]), max_steps=int(g["rtf_budget"]),
+                                  reset_kwargs=dict(init_state=g["rtf_inits"]))
+    finally:
+        torch.set_default_dtype(old)
+    assert len(ros) == int(g["rtf_n"])
+    for i, ro in enumerate(ros):
+        ref_obs = g[f"rtf{i}_obs"]
+        assert len(ro) == ref_obs.shape[0] - 1, (i, len(ro))
+        assert bool(ro.done[-1]) == bool(g[f"rtf{i}_complete"])
+        np.testing.assert_allclose(ro.observations, ref_obs, rtol=tol, atol=tol)
+        np.testing.assert_allclose(ro.actions, g[f"rtf{i}_act"], rtol=max(tol, 1e-6), atol=max(tol, 1e-6))
+        np.testing.assert_allclose(ro.rewards, g[f"rtf{i}_rew"], rtol=tol, atol=tol)
+        np.testing.assert_allclose(ro.th_ddot, g[f"rtf{i}_th_ddot"], rtol=10 * tol, atol=10 * tol)
+        og, rg = ro.env_infos["obs_grad"], ro.env_infos["rew_grad"]
+        assert og.shape == g[f"rtf{i}_obs_grad"].shape and rg.shape == g[f"rtf{i}_rew_grad"].shape
+        sc = max(1.0, np.abs(g[f"rtf{i}_obs_grad"]).max())
+        assert np.abs(og - g[f"rtf{i}_obs_grad"]).max() < 50 * tol * sc
+        assert np.abs(rg - g[f"rtf{i}_rew_grad"]).max() < 50 * tol * max(1.0, np.abs(g[f"rtf{i}_rew_grad"]).max())
+
+
+def test_rollout_tensor_full_kernel_jacobians_equal_autograd_and_sampler():
+    """The one-launch Jacobian route must equal the reference's five-autograd-passes route (forced by hiding the chain
+    from the kernel path), and ParallelRolloutSamplerTensor collects at least `min_steps` steps of such rollouts."""
+    import simurlacra_b200.sampling.rollout_tensor as RT
+    from simurlacra_b200.sampling import ParallelRolloutSamplerTensor, rollout_tensor_full
+
+    env = _wgrad_env(15, False, torch.float64)
+    W = torch.tensor([[0.5, -0.4, 0.3, 0.1]], dtype=torch.float64)
+    policy = lambda o: torch.tanh(o.double() @ W.T.to(o.device))
+    a = rollout_tensor_full(env, policy, bsz=16, max_steps=16 * 25, seed=4)
+    orig = RT._kernel_chain
+    RT._kernel_chain = lambda e: None
+    try:
+        b = rollout_tensor_full(env, policy, bsz=16, max_steps=16 * 25, seed=4)
+    finally:
+        RT._kernel_chain = orig
+    assert len(a) == len(b) and len(a) >= 16
+    for x, y in zip(a, b):
+        np.testing.assert_allclose(x.observations, y.observations, rtol=1e-12, atol=1e-13)
+        np.testing.assert_allclose(x.env_infos["obs_grad"], y.env_infos["obs_grad"], rtol=1e-8, atol=1e-9)
+        np.testing.assert_allclose(x.env_infos["rew_grad"], y.env_infos["rew_grad"], rtol=1e-8, atol=1e-9)
+    assert len({tuple(np.round(r.observations[0], 9)) for r in a}) > 8  # the resets draw different initial states
+    smp = ParallelRolloutSamplerTensor(env, policy, min_steps=500, seed=1, bsz=32)
+    ros = smp.sample()
+    assert sum(len(r) for r in ros) >= 500 and all("obs_grad" in r.env_infos for r in ros)
