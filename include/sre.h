@@ -348,6 +348,30 @@ int sre_qcp_diff_backward(const sre_env_cfg *cfg, const void *params, const void
 int sre_qcp_diff_jacobian(const sre_env_cfg *cfg, const void *params, const void *state, const void *thdd,
                           const void *act, int64_t n, void *jac, void *stream);
 
+/* ---- no-allocation entry point ------------------------------------------------------------------------ */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * sre_qcp_diff_forward followed by sre_qcp_diff_backward in one call (same kernels, same arguments, same results),
+ * with the tape between them -- states real [H+1, N, 4] and thdd real [H+1, N], which the other two entry points take
+ * from the caller -- in a file-scope static device array of SRE_STATIC_TAPE_BYTES that every GPU loading the library
+ * holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); its only
+ * set-up is one cudaGetSymbolAddress per device, on the first call with that device current.
+ * Limit: align256((H+1) * N * 4 * sizeof(real)) + (H+1) * N * sizeof(real) <= SRE_STATIC_TAPE_BYTES (float32: about
+ * 1.67 M (row, env) pairs, e.g. 4096 envs x 400 steps; float64: half of that); larger sizes return SRE_E_ARG with a
+ * message, device ordinals >= SRE_STATIC_MAX_DEVICES return SRE_E_UNSUPPORTED.
+ * Every call on a device shares the one tape: calls that overlap on the GPU (two streams, two host threads) RACE --
+ * serialise them on one stream.  Nothing in the tape has to start at zero (the forward pass writes every element the
+ * adjoint reads), so it is not cleared; it keeps the last call's contents.
+ * Inputs as sre_qcp_diff_forward (params, s0, thdd0, act) and sre_qcp_diff_backward (g_states, g_rew, g_thdd, any of
+ * them NULL = zeros); outputs rew real [H, N] / done uint8 [H, N] (may be NULL), g_s0 real [N, 4], g_act real [H, N],
+ * g_thdd0 real [N] (may be NULL). */
+#define SRE_STATIC_TAPE_BYTES (32u << 20)
+#define SRE_STATIC_MAX_DEVICES 64
+int sre_qcp_diff_grad_static(const sre_env_cfg *cfg, const void *params, const void *s0, const void *thdd0,
+                             const void *act, const void *g_states, const void *g_rew, const void *g_thdd, int64_t n,
+                             int64_t horizon, void *rew, uint8_t *done, void *g_s0, void *g_act, void *g_thdd0,
+                             void *stream);
+
 /* ---- measurement helpers (roofline denominators measured on the box) ---------------------- */
 /* FMA-only kernel: every thread runs `iters` x 32 dependent-free FFMA (dtype F32) or DFMA (F64).
  * Returns FLOPs issued in *flops; time it with CUDA events on `stream`. */

@@ -165,6 +165,8 @@ SIGNATURES = {
     "sre_qcp_diff_forward": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP]),
     "sre_qcp_diff_backward": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP]),
     "sre_qcp_diff_jacobian": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _I64, _VP, _VP]),
+    "sre_qcp_diff_grad_static": (_I, [C.POINTER(EnvCfg), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP,
+                                      _VP, _VP]),
     "sre_bench_fma": (_I, [_I, _I64, _I, _I, _VP, C.POINTER(C.c_double), _VP]),
     "sre_bench_hbm_write": (_I, [_VP, _I64, _VP]),
 }

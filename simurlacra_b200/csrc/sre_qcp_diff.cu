@@ -7,6 +7,8 @@
 //   * dead-zone mask, normal-force mask and sign(x_dot) are constants of the graph (:376-377, :394-396)
 //   * the reward's angle wrap is detached: d theta_err / d th = -1 (:299-306)
 //   * th_ddot carried from stage to stage and from step to step stays attached (:645-652)
+#include <mutex>
+
 #include "sre_host.h"
 
 namespace sre {
@@ -295,6 +297,12 @@ qcp_diff_jacobian_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, c
 
 }  // namespace sre
 
+// ---- tape of sre_qcp_diff_grad_static: no allocation at call time ----------------------------------------------
+// File-scope device memory: every GPU that loads the library holds these SRE_STATIC_TAPE_BYTES until the process exits.
+// In host code `g_static_tape` is only a stand-in for the symbol, NOT a device address: the address comes from
+// cudaGetSymbolAddress, once per device with that device current (static_tape_ptr below).
+static __device__ __align__(256) unsigned char g_static_tape[SRE_STATIC_TAPE_BYTES];
+
 using namespace sre;
 
 static int qcp_check(const sre_env_cfg *cfg) {
@@ -389,3 +397,75 @@ int sre_qcp_diff_jacobian(const sre_env_cfg *cfg, const void *params, const void
 }
 
 }  // extern "C"
+
+// Device address of g_static_tape on the CURRENT device, looked up once per device.  cudaGetSymbolAddress allocates
+// nothing (the array is part of the loaded module); the cache is a fixed table, so the steady state takes one lock.
+static int static_tape_ptr(unsigned char **out) {
+    static std::mutex mtx;
+    static unsigned char *ptrs[SRE_STATIC_MAX_DEVICES] = {nullptr};
+    int dev = -1;
+    SRE_CUDA(cudaGetDevice(&dev));
+    SRE_CHECK_ARG(dev >= 0 && dev < SRE_STATIC_MAX_DEVICES, SRE_E_UNSUPPORTED,
+                  "sre_qcp_diff_grad_static: device ordinal %d beyond the %d the pointer table holds", dev,
+                  SRE_STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(mtx);
+    if (!ptrs[dev]) {
+        void *p = nullptr;
+        SRE_CUDA(cudaGetSymbolAddress(&p, g_static_tape));
+        SRE_CHECK_ARG(p != nullptr && (uintptr_t)p % 256 == 0, SRE_E_UNSUPPORTED,
+                      "sre_qcp_diff_grad_static: cudaGetSymbolAddress gave %p", p);
+        ptrs[dev] = (unsigned char *)p;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+template <typename R>
+static int diff_grad_static(const sre_env_cfg *cfg, const void *params, const void *s0, const void *thdd0,
+                            const void *act, const void *g_states, const void *g_rew, const void *g_thdd, int64_t n,
+                            int64_t horizon, void *rew, uint8_t *done, void *g_s0, void *g_act, void *g_thdd0,
+                            cudaStream_t s) {
+    // tape layout inside the scratch: states [H+1, N, 4] | (256-byte aligned) thdd [H+1, N]
+    const unsigned long long rows = (unsigned long long)horizon + 1ull;
+    const unsigned long long st_bytes = (rows * (unsigned long long)n * 4ull * sizeof(R) + 255ull) & ~255ull;
+    const unsigned long long need = st_bytes + rows * (unsigned long long)n * sizeof(R);
+    SRE_CHECK_ARG(need <= (unsigned long long)SRE_STATIC_TAPE_BYTES, SRE_E_ARG,
+                  "sre_qcp_diff_grad_static: the tape of %lld envs x %lld steps needs %llu bytes, the static scratch "
+                  "holds %llu (SRE_STATIC_TAPE_BYTES); use sre_qcp_diff_forward / _backward with a caller-owned tape",
+                  (long long)n, (long long)horizon, need, (unsigned long long)SRE_STATIC_TAPE_BYTES);
+    unsigned char *base = nullptr;
+    int e = static_tape_ptr(&base);
+    if (e) return e;
+    R *states = (R *)base;
+    R *thdd = (R *)(base + st_bytes);
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    KCfg<R> k;
+    make_kcfg<R>(*cfg, k);
+    // Nothing in the tape has to start at zero: the forward pass writes every (row, env) element the adjoint reads
+    // (rows 0..H of the n envs of THIS call), so the previous call's contents are dead.
+    qcp_diff_forward_kernel<R><<<blocks, 128, 0, s>>>(k, (const R *)params, (const R *)s0, (const R *)thdd0,
+                                                      (const R *)act, n, horizon, states, thdd, (R *)rew, done);
+    SRE_CUDA(cudaGetLastError());
+    qcp_diff_backward_kernel<R><<<blocks, 128, 0, s>>>(k, (const R *)params, states, thdd, (const R *)act,
+                                                       (const R *)g_states, (const R *)g_rew, (const R *)g_thdd, n,
+                                                       horizon, (R *)g_s0, (R *)g_act, (R *)g_thdd0);
+    SRE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sre_qcp_diff_grad_static(const sre_env_cfg *cfg, const void *params, const void *s0, const void *thdd0,
+                                        const void *act, const void *g_states, const void *g_rew, const void *g_thdd,
+                                        int64_t n, int64_t horizon, void *rew, uint8_t *done, void *g_s0, void *g_act,
+                                        void *g_thdd0, void *stream) {
+    int e = qcp_check(cfg);
+    if (e) return e;
+    SRE_CHECK_ARG(s0 && act && g_s0 && g_act && n >= 0 && horizon >= 0, SRE_E_ARG, "NULL pointer or negative size");
+    SRE_CHECK_ARG((uintptr_t)s0 % 16 == 0, SRE_E_ARG, "s0 must be 16-byte aligned");
+    if (n == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cfg->dtype == SRE_F64)
+        return diff_grad_static<double>(cfg, params, s0, thdd0, act, g_states, g_rew, g_thdd, n, horizon, rew, done,
+                                        g_s0, g_act, g_thdd0, s);
+    return diff_grad_static<float>(cfg, params, s0, thdd0, act, g_states, g_rew, g_thdd, n, horizon, rew, done, g_s0,
+                                   g_act, g_thdd0, s);
+}
