@@ -488,6 +488,7 @@ def main():
 
     peaks = measured_peaks()
     fma_peak = measure_fma_peak(E, L, torch, dev, L.F32)
+    FMA_REG.update(scalar=measure_fma_peak(E, L, torch, dev, 3), packed=measure_fma_peak(E, L, torch, dev, 4))
     extras = {}
     clocks = ClockSampler(local)
 
@@ -571,6 +572,20 @@ def diff_setup(E, L, torch, dev, n, h):
     return dcfg, s0_h, act_h
 
 
+FMA_REG = {}  # measured live in main(): FMA rate with three distinct register operands (scalar / packed f32x2), TFLOP/s
+
+
+def reg_operand_fields(achieved):
+    """The FMA-only peak above is reached with operands from immediates / the reuse cache; simulation arithmetic reads three
+    changing registers per FMA, which the register file serves at a lower rate (measured by sre_bench_fma dtype 3 / 4)."""
+    if not FMA_REG:
+        return {}
+    best = max(FMA_REG.values())
+    return dict(peak_register_operands=best, frac_register_operands=achieved / best,
+                peak_register_operands_source="measured live: FFMA / FFMA2 with three distinct changing register operands "
+                                              f"(sre_bench_fma dtype 3: {FMA_REG['scalar']:.1f}, dtype 4: {FMA_REG['packed']:.1f} TFLOP/s)")
+
+
 def c5_rooflines(rate_fwd, rate_fb, peaks, fma_peak, n, h):
     """C5: forward = FP32 FMA (375 FLOP per step); forward + adjoint also moves the 24 B/step tape twice."""
     a_f = rate_fwd * C5_FLOP_FWD / 1e12
@@ -578,12 +593,12 @@ def c5_rooflines(rate_fwd, rate_fb, peaks, fma_peak, n, h):
     tape = rate_fb * 2 * C5_TAPE_BYTES / 1e9
     return dict(workload=f"differentiable QCartPole (sac_wgrad path), RK4 dt=1/20, {n} envs x {h} steps, injected actions",
                 forward=dict(env_steps_per_s=rate_fwd, bound="fp32_fma", achieved=a_f, peak=fma_peak, unit="TFLOP/s",
-                             frac=a_f / fma_peak, flop_per_env_step=C5_FLOP_FWD),
+                             frac=a_f / fma_peak, flop_per_env_step=C5_FLOP_FWD, **reg_operand_fields(a_f)),
                 forward_adjoint=dict(env_steps_per_s=rate_fb, bound="fp32_fma", achieved=a_fb, peak=fma_peak, unit="TFLOP/s",
                                      frac=a_fb / fma_peak, flop_per_env_step=C5_FLOP_FWD + C5_FLOP_BWD,
                                      flop_note="forward 375 (SURVEY 8a) + adjoint 2.5 x 375: the reverse sweep re-evaluates "
                                                "the four RK4 stages from the tape and propagates 5 adjoints through each",
-                                     tape_gbs=tape, tape_frac_hbm=tape / peaks["hbm_gbs"]))
+                                     tape_gbs=tape, tape_frac_hbm=tape / peaks["hbm_gbs"], **reg_operand_fields(a_fb)))
 
 
 def run_diff(E, L, torch, dev, n, h, K, warmup, timed, wall_timed, peaks, fma_peak, clocks, rank, world, dist):

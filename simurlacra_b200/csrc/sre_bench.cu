@@ -45,6 +45,46 @@ __global__ void __launch_bounds__(256) fma2_kernel(long long iters, float seed, 
     if (s == 123.456f) sink[0] = s;
 }
 
+// FMA with three DISTINCT, changing register operands per instruction (acc[i] = acc[i+1] * acc[i+2] + acc[i]): what
+// simulation code issues -- no operand comes from an immediate, the constant bank or the operand-reuse cache, so the
+// register file has to deliver three reads per lane and instruction.  PACKED: the same on fma.rn.f32x2.
+template <bool PACKED> __global__ void __launch_bounds__(256) fma3reg_kernel(long long iters, float seed, float *sink) {
+    if constexpr (!PACKED) {
+        float acc[32];
+#pragma unroll
+        for (int i = 0; i < 32; i++) acc[i] = 1.0f + 1e-7f * (seed + (float)(threadIdx.x + i));
+        for (long long it = 0; it < iters; it++) {
+#pragma unroll
+            for (int i = 0; i < 32; i++)
+                asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc[i]) : "f"(acc[(i + 11) & 31]), "f"(acc[(i + 22) & 31]));
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i++) s += acc[i];
+        if (s == 123.456f) sink[0] = s;
+    } else {
+        unsigned long long acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            float lo = 1.0f + 1e-7f * (seed + (float)(threadIdx.x + 2 * i)), hi = lo + 1e-7f;
+            asm("mov.b64 %0, {%1, %2};" : "=l"(acc[i]) : "f"(lo), "f"(hi));
+        }
+        for (long long it = 0; it < iters; it++) {
+#pragma unroll
+            for (int i = 0; i < 16; i++)
+                asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc[i]) : "l"(acc[(i + 5) & 15]), "l"(acc[(i + 11) & 15]));
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            float lo, hi;
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc[i]));
+            s += lo + hi;
+        }
+        if (s == 123.456f) sink[0] = s;
+    }
+}
+
 __global__ void __launch_bounds__(256) hbm_write_kernel(float4 *dst, long long n_vec) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const float4 v = make_float4(1.f, 2.f, 3.f, 4.f);
@@ -58,9 +98,11 @@ using namespace sre;
 extern "C" {
 
 int sre_bench_fma(int dtype, int64_t iters, int blocks, int threads, float *sink, double *flops, void *stream) {
-    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64 || dtype == 2, SRE_E_DTYPE, "unknown dtype %d", dtype);
+    SRE_CHECK_ARG(dtype == SRE_F32 || dtype == SRE_F64 || (dtype >= 2 && dtype <= 4), SRE_E_DTYPE, "unknown dtype %d", dtype);
     SRE_CHECK_ARG(iters > 0 && blocks > 0 && threads > 0 && threads <= 256 && sink, SRE_E_ARG, "bad launch shape");
     if (dtype == 2) fma2_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
+    else if (dtype == 3) fma3reg_kernel<false><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
+    else if (dtype == 4) fma3reg_kernel<true><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
     else if (dtype == SRE_F32) fma_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5f, sink);
     else fma_kernel<double><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, 0.5, reinterpret_cast<double *>(sink));
     if (flops) *flops = 2.0 * 32.0 * (double)iters * (double)blocks * (double)threads;

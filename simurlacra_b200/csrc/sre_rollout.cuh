@@ -22,9 +22,6 @@ namespace sre {
 #ifndef SRE_COOP_MAX_LANES
 #define SRE_COOP_MAX_LANES 5  // up to this many restarting lanes of a warp draw their parameters cooperatively
 #endif
-#ifndef SRE_PREP_PERIOD
-#define SRE_PREP_PERIOD 32  // rows between two convergent refills of the prepared episode starts (power of two)
-#endif
 #define SRE_PV_TC 1000    // [do,64,64,da] tanh, hidden layer on the tensor cores, 3 x TF32 (sre_policy_tc.cuh)
 #define SRE_PV_TC1 1001   // the same, single TF32 pass
 
@@ -278,19 +275,25 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             failed_ep = false;
         }
     };
-    // Prepared episode starts (auto-reset sampling).  What an episode start computes depends only on (seed, env, episode):
-    // every PREP_PERIOD rows the warp computes the NEXT start of all lanes whose slot is empty in ONE convergent pass and
-    // parks it in shared memory; a lane that restarts then only loads its slot (a few dozen instructions at one
-    // active lane instead of the whole DR draw + derive + init + kinematics).  Same values, same order of episodes; a
-    // lane that restarts twice within a period takes the direct path.  `ready` is warp-uniform: bit l = slot of lane l
-    // holds the start of episode `episode + 1` of that lane.
-    constexpr int PREP_PERIOD = SRE_PREP_PERIOD;
+    // Prepared episode starts (auto-reset sampling).  What an episode start computes depends only on (seed, env, episode),
+    // so it can be computed ahead of time and parked in shared memory; a lane that restarts then only loads its slot (a
+    // few dozen instructions at one active lane instead of the whole DR draw + derive + init + kinematics).  The slots
+    // are filled in CONVERGENT passes whose cost does not depend on how many lanes take part (the draws run lane-parallel,
+    // QBB's kinematics solves of up to 16 lanes share one 100-iteration loop): one pass right after the first start, and
+    // from then on ON DEMAND -- when a lane restarts and finds its slot empty, the pass that computes its start also
+    // fills the empty slot of every other running lane of the warp with that lane's NEXT start.  Every expensive pass
+    // therefore serves as many episode starts as the warp has open, whatever the episode lengths are (a pass every
+    // PREP_PERIOD rows, the first design, left lanes that restart twice within a period on a divergent direct path:
+    // 1.7 k warp-instructions on most rows once episodes are shorter than the period).  Same values, same order of
+    // episodes.  `ready` is warp-uniform: bit l = slot of lane l holds the start of episode `episode + 1` of that lane.
     const bool prep = io.prep_slots && io.auto_reset;
     unsigned ready = 0u;
-    auto prepare_slots = [&](unsigned need) {
+    // need: lanes whose slot is filled by this pass; now: the subset that restarts in this row (their `episode` is
+    // already the one to start), the others get their next one
+    auto prepare_slots = [&](unsigned need, unsigned now) {
         Lane<KIND, R> P;
         const bool mine = (need >> lane) & 1u;
-        start_episode(P, episode + 1u, mine, need, false);
+        start_episode(P, episode + (((now >> lane) & 1u) ? 0u : 1u), mine, need, false);
         if (mine) P.store_slot(slot, 32);
         ready |= need;
         __syncwarp();
@@ -332,7 +335,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     };
 
     start_episode(L, episode, valid, __ballot_sync(0xffffffffu, valid), true);
-    if (prep) prepare_slots(__ballot_sync(0xffffffffu, valid));
+    if (prep) prepare_slots(__ballot_sync(0xffffffffu, valid), 0u);
 
     for (long long row = 0; row < T; row++) {
         // the record of this row goes straight into the warp's staging tile (the pre-step fields before the step: nothing
@@ -467,6 +470,11 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                     }
                 }
                 const unsigned rs = __ballot_sync(0xffffffffu, restart);
+                if (prep && (rs & ~ready) && row < T - 2) {
+                    // a restarting lane has no prepared start: one pass for it and for every other empty slot
+                    const unsigned running = __ballot_sync(0xffffffffu, lane_state != IDLE);
+                    prepare_slots(running & ~ready, rs & ~ready);
+                }
                 const unsigned fast = rs & ready;
                 if (fast) {
                     if ((fast >> lane) & 1u) {
@@ -488,10 +496,6 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 warp_store_row<R>(stage, static_cast<R *>(io.traj) + (row * N + warp_env0) * W, n_valid_lanes * W, vec_ok,
                                   lane);
             __syncwarp();
-        }
-        if (prep && (row & (PREP_PERIOD - 1)) == PREP_PERIOD - 1 && row < T - 2) {
-            const unsigned need = __ballot_sync(0xffffffffu, lane_state != IDLE) & ~ready;
-            if (need) prepare_slots(need);
         }
         if (want_flag && valid) io.row_flag[row * N + n] = flag;
         if (!TC && !record && !want_flag) {

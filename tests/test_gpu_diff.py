@@ -223,3 +223,31 @@ def test_rollout_tensor_full_kernel_jacobians_equal_autograd_and_sampler():
     smp = ParallelRolloutSamplerTensor(env, policy, min_steps=500, seed=1, bsz=32)
     ros = smp.sample()
     assert sum(len(r) for r in ros) >= 500 and all("obs_grad" in r.env_infos for r in ros)
+
+
+@pytest.mark.parametrize("simple", [False, True])
+def test_packed_pair_kernels_agree_with_the_scalar_kernels(E, simple, monkeypatch):
+    """The float forward pass runs two environments per thread on packed f32x2 arithmetic (qcp_diff_forward2_kernel);
+    SRE_DIFF_SCALAR=1 forces the one-environment kernel.  Same formulas, so the tape agrees to float round-off over a
+    short horizon (the swing-up amplifies differences later)."""
+    H, N = 40, 4096
+    cfg = _cfg(E, simple, torch.float32)
+    g = torch.Generator().manual_seed(5)
+    s0 = ((torch.rand(N, 4, generator=g) - 0.5) * torch.tensor([0.4, 6.0, 1.0, 4.0])).to(DEV)
+    act = ((torch.rand(H, N, generator=g) - 0.5) * 16.0).to(DEV)
+    thdd0 = (torch.rand(N, generator=g) - 0.5).to(DEV)
+
+    def run():
+        return E.qcp_diff_forward(cfg, None, s0, act, thdd0=thdd0)
+
+    packed = [x.cpu().numpy() for x in run()]
+    monkeypatch.setenv("SRE_DIFF_SCALAR", "1")
+    scalar = [x.cpu().numpy() for x in run()]
+    for name, a, b, tol in zip(("states", "thdd", "rew", "done"), packed, scalar,
+                               (2e-4, 2e-2, 2e-4, 0)):
+        if name == "done":
+            assert (a != b).mean() < 1e-4
+            continue
+        scale = max(np.abs(b).max(), 1.0)
+        err = np.abs(a.astype(np.float64) - b).max() / scale
+        assert err < tol, (name, err)
