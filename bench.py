@@ -256,14 +256,20 @@ def measured_peaks():
     return dict(hbm_gbs=6650.0, bf16_tflops=1400.0, source="fallback")
 
 
-def ncu_traffic(key):
-    """dram bytes read + written per launch of a kernel from the committed ncu summaries (profiles/r02_traffic.json,
-    written by tools/ncu_traffic.py from `ncu --set full` captures), or None: nothing is pasted into this file."""
+def ncu_traffic(key, units_per_launch=None):
+    """dram bytes read + written per launch of a kernel from the committed ncu captures (profiles/r02_traffic.json, written
+    by tools/ncu_traffic.py from `ncu --set full` reports), or None: nothing is pasted into this file.  A capture taken at
+    another launch size is scaled by the work units (env-steps / rows) of the launch timed here; the source says so."""
     path = osp.join(ROOT, "profiles", "r02_traffic.json")
     if not osp.exists(path):
         return None, None
     d = json.load(open(path)).get(key)
-    return (d["dram_bytes"], d["source"]) if d else (None, None)
+    if not d:
+        return None, None
+    if units_per_launch is None or abs(units_per_launch - d["units"]) < 1e-6 * d["units"]:
+        return d["dram_bytes"], d["source"]
+    return (d["bytes_per_unit"] * units_per_launch,
+            d["source"] + f"; {d['bytes_per_unit']:.4g} B per unit scaled to the {units_per_launch:.4g} units of this launch")
 
 
 def time_launches(torch, fn, k, flush):
@@ -354,12 +360,13 @@ def rate_of(stats_list, t, L):
     return steps / t, eps / max(1, len(stats_list))
 
 
-def roofline_for(wl, rate_per_gpu, peaks, fma_peak, n_envs):
-    """The roofline object of a rollout workload at `rate_per_gpu` env-steps/s."""
+def roofline_for(wl, rate_per_gpu, peaks, fma_peak, n_envs, steps_per_launch=None):
+    """The roofline object of a rollout workload at `rate_per_gpu` env-steps/s (steps_per_launch: env-steps one launch
+    processed, for the ncu traffic figure)."""
     if wl["record"]:
         b = RECORD_BYTES[wl["name"]]
         gbs = rate_per_gpu * b / 1e9
-        tr, src = ncu_traffic(f"{wl['name']}_rec")
+        tr, src = ncu_traffic(f"{wl['name']}_rec", steps_per_launch)
         return dict(bound="hbm", achieved=gbs, peak=peaks["hbm_gbs"], unit="GB/s", frac=gbs / peaks["hbm_gbs"],
                     traffic=tr, traffic_source=src, bytes_per_env_step=b,
                     peak_source=f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']})",
@@ -377,7 +384,7 @@ def roofline_for(wl, rate_per_gpu, peaks, fma_peak, n_envs):
     passes = 3 if wl["prec"] == 1 else 1
     t_peak = peaks["bf16_tflops"] / 2
     t_iss = rate_per_gpu * passes * 2 * hid * hid / 1e12
-    tr, src = ncu_traffic(f"{wl['name']}_tc")
+    tr, src = ncu_traffic(f"{wl['name']}_tc", steps_per_launch)
     return dict(bound="tensor", achieved=achieved, peak=t_peak, unit="TFLOP/s", frac=achieved / t_peak, traffic=tr,
                 traffic_source=src, flop_per_env_step=wl["flop"], issued=t_iss, frac_issued=t_iss / t_peak,
                 peak_source=f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']}) / 2: kind::tf32 runs at half "
@@ -529,7 +536,7 @@ def main():
                              d2h_bytes_per_step=int(N * 8 + 64),
                              call="ParallelRolloutSampler.sample_batch(N): policy parameters from pinned host memory, "
                                   "returns + lengths + statistics read back to the host"),
-                    roofline=roofline_for(wl, value / world, peaks, fma_peak, N),
+                    roofline=roofline_for(wl, value / world, peaks, fma_peak, N, steps_per_launch=value / world * t_dev / K),
                     config=dict(workload=wl["label"], envs_per_gpu=N, horizon=wl["H"], auto_reset=True,
                                 trajectory="full records in HBM" if wl["record"] else "returns+lengths+stats",
                                 policy_hidden_layer={0: "fp32 FMA (CUDA cores)", 1: "tcgen05 3xTF32 split (fp32-level accuracy)",
@@ -698,14 +705,14 @@ def run_extras(args, E, L, torch, dev, timed, wall_timed, peaks, fma_peak, flush
         c3 = {}
         for prec, nm in ((1, "tcgen05_tf32x3"), (0, "fp32_fma")):
             wl, rate, eps, ms = measure("qcp", 1 << 22, prec=prec, k=2)
-            c3[nm] = dict(roofline_for(wl, rate, peaks, fma_peak, 1 << 22), env_steps_per_s=rate, ms_per_launch=ms,
+            c3[nm] = dict(roofline_for(wl, rate, peaks, fma_peak, 1 << 22, steps_per_launch=rate * ms * 1e-3), env_steps_per_s=rate, ms_per_launch=ms,
                           episodes_per_launch=eps)
             c3[nm].pop("fp32_view", None)
         c3["workload"] = wl["label"] + ", 4194304 envs"
         out["roofline_c3"] = c3
     if args.workload != "qbb":
         wl, rate, eps, ms = measure("qbb", 1 << 21, k=2)
-        out["roofline_traj"] = dict(roofline_for(wl, rate, peaks, fma_peak, 1 << 21), env_steps_per_s=rate, ms_per_launch=ms,
+        out["roofline_traj"] = dict(roofline_for(wl, rate, peaks, fma_peak, 1 << 21, steps_per_launch=rate * ms * 1e-3), env_steps_per_s=rate, ms_per_launch=ms,
                                     episodes_per_launch=eps, workload=wl["label"] + ", 2097152 envs")
 
     # ---- C5: differentiable cart-pole

@@ -672,4 +672,97 @@ template <int IN, int OUT, bool SINGLE_PASS = false> struct FnnTC2 {
     }
 };
 
+// ---- [IN, 16, 16, OUT] in the production (float) build: thread per environment, everything in registers ----------
+// The warp-tiled layout above pays for its activation exchange through shared memory and the transpose-reduce with
+// ~730 instructions per forward pass at HID = 16 (profiles/r02_c_c4_*: 57 % of the C4 step for 416 multiply-adds).  At
+// this width a lane holds the whole network state itself: 8 packed accumulator pairs per layer, weights as broadcast
+// LDS.128 of the transposed matrices (four per input unit), the activation as the scalar operand of FFMA2, tanh four at a
+// time with one shared reciprocal.  64 + 128 + 8 OUT FFMA2, 2 x 16 tanh, ~110 LDS.128: ~450 instructions.
+template <int IN, int OUT> struct FnnTiled<IN, 16, OUT, true> {
+    static constexpr int HID = 16;
+    static constexpr int OP = (OUT + 1) / 2;                 // output pairs
+    static constexpr int OFF_W1T = 0;                        // [IN][16]
+    static constexpr int OFF_B1 = OFF_W1T + IN * HID;        // [16]
+    static constexpr int OFF_W2T = OFF_B1 + HID;             // [16 k][16 j]
+    static constexpr int OFF_B2 = OFF_W2T + HID * HID;       // [16]
+    static constexpr int OFF_W3T = OFF_B2 + HID;             // [16 k][2 OP]
+    static constexpr int OFF_B3 = OFF_W3T + HID * 2 * OP;    // [2 OP]
+    static constexpr int W_FLOATS = ((OFF_B3 + 2 * OP + 3) / 4) * 4;
+    static constexpr int H1S_FLOATS = 0;
+    static constexpr int WARPS = 8;
+    static constexpr int SMEM_FLOATS = W_FLOATS;
+    static constexpr float PRE = SRE_TANH_PRESCALE;
+
+    SRE_DEV static void stage(const float *__restrict__ w, float *sm) {
+        const float *W1 = w, *b1 = W1 + IN * HID, *W2 = b1 + HID, *b2 = W2 + HID * HID, *W3 = b2 + HID,
+                    *b3 = W3 + OUT * HID;
+        for (int i = threadIdx.x; i < IN * HID; i += blockDim.x) sm[OFF_W1T + (i % IN) * HID + i / IN] = PRE * W1[i];
+        for (int i = threadIdx.x; i < HID * HID; i += blockDim.x) sm[OFF_W2T + (i % HID) * HID + i / HID] = PRE * W2[i];
+        for (int i = threadIdx.x; i < HID; i += blockDim.x) { sm[OFF_B1 + i] = PRE * b1[i]; sm[OFF_B2 + i] = PRE * b2[i]; }
+        for (int i = threadIdx.x; i < HID * 2 * OP; i += blockDim.x) {
+            const int k = i / (2 * OP), o = i % (2 * OP);
+            sm[OFF_W3T + i] = o < OUT ? W3[o * HID + k] : 0.f;
+        }
+        for (int i = threadIdx.x; i < 2 * OP; i += blockDim.x) sm[OFF_B3 + i] = i < OUT ? b3[i] : 0.f;
+    }
+
+    // one layer into 16 units: acc[8] = {b[2p], b[2p+1]} + sum_i wT[i][2p..2p+1] * x_i
+    template <int NI> SRE_DEV static void layer16(const float *wT, const float *b, const float *x, unsigned long long *acc) {
+        const float4 *bv = reinterpret_cast<const float4 *>(b);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float4 v = bv[q];
+            acc[2 * q] = pack2(v.x, v.y);
+            acc[2 * q + 1] = pack2(v.z, v.w);
+        }
+#pragma unroll
+        for (int i = 0; i < NI; i++) {
+            const float4 *wv = reinterpret_cast<const float4 *>(wT + i * HID);
+            const unsigned long long xi = pack2(x[i], x[i]);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float4 w = wv[q];
+                acc[2 * q] = fma2(pack2(w.x, w.y), xi, acc[2 * q]);
+                acc[2 * q + 1] = fma2(pack2(w.z, w.w), xi, acc[2 * q + 1]);
+            }
+        }
+    }
+    SRE_DEV static void tanh16(unsigned long long *a, float *h) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            tanh4_prescaled(a[2 * q], a[2 * q + 1]);
+            unpack2(a[2 * q], h[4 * q], h[4 * q + 1]);
+            unpack2(a[2 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+        }
+    }
+
+    // same interface as the tiled variants (h1s / lane unused): x = observation of the lane's own environment
+    SRE_DEV static void forward(const float *sm, float *, const float *x, float *out, int) {
+        unsigned long long a[8];
+        float h1[16], h2[16];
+        layer16<IN>(sm + OFF_W1T, sm + OFF_B1, x, a);
+        tanh16(a, h1);
+        layer16<HID>(sm + OFF_W2T, sm + OFF_B2, h1, a);
+        tanh16(a, h2);
+        unsigned long long o[OP];
+        const unsigned long long *b3 = reinterpret_cast<const unsigned long long *>(sm + OFF_B3);
+#pragma unroll
+        for (int p = 0; p < OP; p++) o[p] = b3[p];
+#pragma unroll
+        for (int k = 0; k < HID; k++) {
+            const unsigned long long hk = pack2(h2[k], h2[k]);
+            const unsigned long long *w = reinterpret_cast<const unsigned long long *>(sm + OFF_W3T + k * 2 * OP);
+#pragma unroll
+            for (int p = 0; p < OP; p++) o[p] = fma2(w[p], hk, o[p]);
+        }
+#pragma unroll
+        for (int p = 0; p < OP; p++) {
+            float lo, hi;
+            unpack2(o[p], lo, hi);
+            out[2 * p] = lo;
+            if (2 * p + 1 < OUT) out[2 * p + 1] = hi;
+        }
+    }
+};
+
 }  // namespace sre

@@ -41,6 +41,7 @@ struct KIO {
     int *status;
     int idle_policy;
     int prep_slots;  // host: shared memory holds one prepared episode start per lane (auto-reset sampling, see the kernel)
+    int stage_bufs;  // host: 1, or 2 = the warp's record tile is double-buffered and leaves with cp.async.bulk (see the kernel)
 };
 
 template <int KIND, typename R> struct Rec {
@@ -68,6 +69,17 @@ template <typename R> SRE_DEV void warp_store_row(const R *stage, R *g, int n_va
     }
 }
 
+// Bulk (TMA) store of a warp's record tile: ONE instruction issued by one lane moves the `bytes` contiguous bytes from
+// shared to global memory asynchronously (UBLKCP in SASS), instead of a 6-trip LDS.128 / STG.128 loop on every lane.
+// bytes % 16 == 0, both addresses 16-byte aligned.  The writers fence their generic-proxy stores first (fence_async_smem).
+SRE_DEV void bulk_store_tile(void *gdst, const void *ssrc, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// wait until at most `N` of this thread's bulk groups are still READING shared memory
+template <int N> SRE_DEV void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+
 SRE_DEV void atomic_min_double(double *addr, double v) {
     unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
     unsigned long long old = *a, assumed;
@@ -91,10 +103,13 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
 #ifndef SRE_TC_BLOCKS
 #define SRE_TC_BLOCKS 4  // resident CTAs (= UMMA tiles) per SM of the tensor-core variant: 128 TMEM columns each
 #endif
+#ifndef SRE_FNN_BLOCKS
+#define SRE_FNN_BLOCKS 2  // resident 256-thread CTAs per SM of the fused-FNN (CUDA-core) variants of the float build
+#endif
 template <typename R, int PV> struct LaunchShape {
     static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile
     static constexpr int THREADS = TC ? 128 : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128);
-    static constexpr int MIN_BLOCKS = TC ? SRE_TC_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? 2 : 1);
+    static constexpr int MIN_BLOCKS = TC ? SRE_TC_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? SRE_FNN_BLOCKS : 1);
 };
 
 template <int KIND, typename R> SRE_DEV float qbb_plate_ang(R arm_radius, R plate_length, R th_in) {
@@ -131,8 +146,9 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     float *sm_w = reinterpret_cast<float *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool has_stage = !(PV >= SRE_PV_TC) || (MODE == SRE_MODE_GENERIC ? io.traj != nullptr : MODE == SRE_MODE_PLAIN_REC);
-    const size_t stage_bytes = has_stage ? (size_t)(blockDim.x / 32) * 32 * W * sizeof(R) : 0;
-    R *stage = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * 32 * W;
+    const int n_bufs = io.stage_bufs == 2 ? 2 : 1;
+    const size_t stage_bytes = has_stage ? (size_t)n_bufs * (blockDim.x / 32) * 32 * W * sizeof(R) : 0;
+    R *const stage0 = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float)) + (size_t)warp * n_bufs * 32 * W;
     constexpr int NSLOT = Lane<KIND, R>::NSLOT;
     // prepared episode starts: [warp][field][lane]
     R *slot = reinterpret_cast<R *>(smem_raw + (size_t)pol.smem_floats * sizeof(float) + stage_bytes) +
@@ -340,7 +356,12 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     for (long long row = 0; row < T; row++) {
         // the record of this row goes straight into the warp's staging tile (the pre-step fields before the step: nothing
         // of a record stays in registers across the dynamics)
+        R *const stage = stage0 + ((n_bufs == 2 && (row & 1)) ? 32 * W : 0);
         R *my_rec = stage + lane * W;
+        if (n_bufs == 2 && record) {  // the bulk store of two rows ago has to be done reading this buffer
+            if (lane == 0) bulk_wait_read<1>();
+            __syncwarp();
+        }
         unsigned char flag = SRE_ROW_IDLE;
 
         bool restart = false, closed = false, closed_complete = false;
@@ -491,11 +512,17 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
 
         if (record) {
-            __syncwarp();
-            if (n_valid_lanes > 0)
-                warp_store_row<R>(stage, static_cast<R *>(io.traj) + (row * N + warp_env0) * W, n_valid_lanes * W, vec_ok,
-                                  lane);
-            __syncwarp();
+            R *const gdst = static_cast<R *>(io.traj) + (row * N + warp_env0) * W;
+            const unsigned tile_bytes = (unsigned)(n_valid_lanes * W * sizeof(R));
+            if (n_bufs == 2 && (tile_bytes & 15u) == 0u) {
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0 && tile_bytes) bulk_store_tile(gdst, stage, tile_bytes);
+            } else {
+                __syncwarp();
+                if (n_valid_lanes > 0) warp_store_row<R>(stage, gdst, n_valid_lanes * W, vec_ok, lane);
+                __syncwarp();
+            }
         }
         if (want_flag && valid) io.row_flag[row * N + n] = flag;
         if (!TC && !record && !want_flag) {
@@ -503,6 +530,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             if (__ballot_sync(0xffffffffu, lane_state != IDLE) == 0u) break;
         }
     }
+    if (n_bufs == 2 && lane == 0) bulk_wait_read<0>();  // shared memory must outlive the last bulk stores
 #ifndef SRE_TC_TRACE
     if (valid && io.status) io.status[n] = status;
 #endif
@@ -531,12 +559,20 @@ static int launch_rollout_mode(const KCfg<R> &cfg, const KDistr &distr, const KP
     constexpr int W = Rec<KIND, R>::W;
     const int threads = LaunchShape<R, PV>::THREADS;
     const long long blocks = (io_in.n_envs + threads - 1) / threads;
-    size_t smem = (size_t)pol.smem_floats * sizeof(float) + (size_t)(threads / 32) * 32 * W * sizeof(R);
+    KIO io2 = io_in;
+    const size_t tile_bytes = (size_t)(threads / 32) * 32 * W * sizeof(R);
+    // record tiles leave with bulk stores from a double-buffered stage when the rows are 16-byte aligned in `traj`
+    // (SRE_NO_BULK=1: the LDS / STG loop, for A/B measurements).  Measured: C4 (QBB, 256-thread CTAs) 1.78e10 -> 2.01e10
+    // env-steps/s; the tensor-core variants (128-thread CTAs, four per SM) lose 3 % to the fence + wait and keep the loop.
+    const char *nobulk = getenv("SRE_NO_BULK");
+    io2.stage_bufs = (PV < SRE_PV_TC && io_in.traj && ((size_t)io_in.n_envs * W * sizeof(R)) % 16 == 0 && (32 * W * sizeof(R)) % 16 == 0 &&
+                      reinterpret_cast<size_t>(io_in.traj) % 16 == 0 && !(nobulk && nobulk[0] == '1'))
+                         ? 2 : 1;
+    size_t smem = (size_t)pol.smem_floats * sizeof(float) + io2.stage_bufs * tile_bytes;
     if (PV >= SRE_PV_TC && !io_in.traj) smem = 0;  // the staging area is only needed when records are written
     if (PV >= SRE_PV_TC) smem += FnnTC2<Env<KIND, R>::DO, Env<KIND, R>::DA>::SMEM_BYTES;
     // prepared episode starts: only where they pay (auto-reset sampling with something to compute per episode) and
     // where the resident CTAs of an SM still fit its shared memory
-    KIO io2 = io_in;
     const size_t slot_bytes = (size_t)threads * Lane<KIND, R>::NSLOT * sizeof(R);
     const char *noprep = getenv("SRE_NO_PREP");
     io2.prep_slots = io_in.auto_reset && !(noprep && noprep[0] == '1') &&

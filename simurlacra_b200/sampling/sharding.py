@@ -3,7 +3,7 @@ Multi-GPU plumbing of the sampler: environments (rollout indices) ar
 with NO exchange during the horizon -- the Philox key uses the GLOBAL rollout index, so any split over ranks yields
 the same rollouts (the analogue of the reference's "same result for 1, 2 or 4 workers",
 Pyrado/tests/test_sampling.py:594-646).  Collectives appear only after a `sample()`:
-  - one all-reduce (SUM) of the small statistics vector + one MIN / MAX all-reduce (what the learner logs,
+  - one all-gather of the 64-byte statistics vector, combined locally into sums / min / max (what the learner logs,
     algorithms/step_based/actor_critic.py:115-121)
   - an optional all-gather of per-rollout returns / lengths (ragged over ranks -> padded)
 Works with NCCL on GPUs and with gloo on CPU tensors (tests).
@@ -31,13 +31,18 @@ def shard_range(n_total: int, rank: int, world_size: int) -> Tuple[int, int]:
 
 
 def allreduce_stats(stats: torch.Tensor, group=None) -> torch.Tensor:
-    """In-place all-reduce of a [SRE_N_STATS] float64 statistics vector: sums for the first six, min / max after."""
-    if world(group)[1] == 1:
+    """In-place reduction of a [SRE_N_STATS] float64 statistics vector over the ranks: sums for the first six entries, min /
+    max after.  ONE collective: the 64-byte vectors are all-gathered and combined locally (sum, min and max would need
+    three all-reduces; at this size a collective is pure launch latency)."""
+    ws = world(group)[1]
+    if ws == 1:
         return stats
-    dist.all_reduce(stats[: L.STAT_MIN_RET], op=dist.ReduceOp.SUM, group=group)
-    mn, mx = stats[L.STAT_MIN_RET: L.STAT_MIN_RET + 1], stats[L.STAT_MAX_RET: L.STAT_MAX_RET + 1]
-    dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
-    dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+    flat = torch.empty(ws * stats.shape[0], dtype=stats.dtype, device=stats.device)  # flat: gloo wants the concatenated form
+    dist.all_gather_into_tensor(flat, stats.contiguous(), group=group)
+    allv = flat.view(ws, stats.shape[0])
+    stats[: L.STAT_MIN_RET] = allv[:, : L.STAT_MIN_RET].sum(dim=0)
+    stats[L.STAT_MIN_RET] = allv[:, L.STAT_MIN_RET].min()
+    stats[L.STAT_MAX_RET] = allv[:, L.STAT_MAX_RET].max()
     return stats
 
 

@@ -87,7 +87,10 @@ def test_grouped_launch_equals_one_launch_per_set(E, dtype):
                 assert torch.equal(g["state"][:, sl], s["state"]) and torch.equal(g["ret"][sl], s["ret"])
             else:
                 assert torch.equal(g["length"][sl], s["length"])
-                assert float((g["state"][:, sl] - s["state"]).abs().max()) < 1e-3  # float32 policy on both builds
+                # float32 policy on both builds (generic FNN / tanhf against the register-resident FNN16 / ex2-based tanh):
+                # round-off amplified over 60 swing-up steps, measured against the largest state entry (velocities ~ 20)
+                scale = max(1.0, float(s["state"].abs().max()))
+                assert float((g["state"][:, sl] - s["state"]).abs().max()) < 1e-3 * scale
 
 
 @pytest.mark.parametrize("sizes,prec,R", [([6, 64, 64, 1], L.PREC_TF32X3, 128), ([6, 64, 64, 1], L.PREC_TF32X3, 384),
