@@ -157,6 +157,34 @@ typedef struct sre_task {
 
 /* One batch of identical environments: ctor arguments of SimPyEnv (environments/pysim/base.py:47) plus the
  * wrappers that are fused into the kernels. */
+/* Stateful / shape-changing step-path wrappers run INSIDE sre_rollout (one wrapper state per environment lane, kept
+ * for the whole launch).  Order of the observation path, innermost first:
+ *   observe -> ObsVelFiltWrapper -> DownsamplingWrapper (mean) -> ObsPartialWrapper -> StateAugmentationWrapper -> policy
+ * and of the action path:  policy -> {Downsampling hold, ActDelay (outer)} -> ActNormWrapper -> ActDelay (inner) -> env.
+ * The recorded observation is the policy's (first min(n_in, DO) entries); the recorded action stays the policy's.
+ * sre_step / sre_reset reject a cfg with any of these set (SRE_E_UNSUPPORTED): between step launches the host applies them. */
+#define SRE_MAX_DELAY 8
+#define SRE_MAX_DOWN 8
+#define SRE_MAX_VF 4
+#define SRE_MAX_AUG 8
+typedef struct sre_step_wrappers {
+    int32_t act_delay;       /* ActDelayWrapper._process_act (environment_wrappers/action_delay.py:97-110): the action of
+                              * `act_delay` steps ago reaches the env, the queue holds zeros after a reset; 0: off */
+    int32_t act_delay_inner; /* 1: the wrapper sits inside ActNormWrapper (env units), 0: outside (policy units) */
+    int32_t delay_first;     /* 1: ActDelay (outer) is applied before the Downsampling hold, 0: after it */
+    int32_t downsample;      /* DownsamplingWrapper (downsampling.py:134-162): every factor-th action is held, the
+                              * observation is the mean over the last `factor` observations; <= 1: off */
+    int32_t obs_keep_mask;   /* ObsPartialWrapper (observation_partial.py:63-75): bit i = entry i is kept; 0: all */
+    int32_t vf_n;            /* ObsVelFiltWrapper (observation_velfilter.py:107-145): number of (pos, vel) pairs */
+    int32_t vf_pos[SRE_MAX_VF]; /* state index of the position */
+    int32_t vf_vel[SRE_MAX_VF]; /* observation index that is replaced by the filtered velocity */
+    double vf_b0, vf_b1, vf_a1, vf_zi; /* first-order filter y = b0 x + z, z' = b1 x - a1 y (a0 = 1), z(reset) = zi x */
+    int32_t n_aug;           /* StateAugmentationWrapper (state_augmentation.py:75-88): appended domain parameters */
+    int32_t aug_fixed;       /* append aug_nominal instead of the episode's values */
+    int32_t aug_param[SRE_MAX_AUG];
+    double aug_nominal[SRE_MAX_AUG];
+} sre_step_wrappers;
+
 typedef struct sre_env_cfg {
     int32_t kind;
     int32_t dtype;
@@ -185,6 +213,7 @@ typedef struct sre_env_cfg {
     double obs_ub[SRE_MAX_DO];
     double env_act_noise_std[SRE_MAX_DA];
     double env_act_noise_mean[SRE_MAX_DA];
+    sre_step_wrappers wrap; /* stateful step-path wrappers of the persistent rollout (all zero: none) */
 } sre_env_cfg;
 
 /* DomainParam (domain_randomization/domain_parameter.py:46): float32 sample -> clamp -> optional round */

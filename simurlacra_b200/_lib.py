@@ -49,6 +49,32 @@ class Task(C.Structure):
     ]
 
 
+MAX_DELAY, MAX_DOWN, MAX_VF, MAX_AUG = 8, 8, 4, 8
+
+
+class StepWrappers(C.Structure):
+    """sre_step_wrappers: the stateful step-path wrappers the persistent rollout kernel runs per lane."""
+
+    _fields_ = [
+        ("act_delay", C.c_int32),
+        ("act_delay_inner", C.c_int32),
+        ("delay_first", C.c_int32),
+        ("downsample", C.c_int32),
+        ("obs_keep_mask", C.c_int32),
+        ("vf_n", C.c_int32),
+        ("vf_pos", C.c_int32 * MAX_VF),
+        ("vf_vel", C.c_int32 * MAX_VF),
+        ("vf_b0", C.c_double),
+        ("vf_b1", C.c_double),
+        ("vf_a1", C.c_double),
+        ("vf_zi", C.c_double),
+        ("n_aug", C.c_int32),
+        ("aug_fixed", C.c_int32),
+        ("aug_param", C.c_int32 * MAX_AUG),
+        ("aug_nominal", C.c_double * MAX_AUG),
+    ]
+
+
 class EnvCfg(C.Structure):
     _fields_ = [
         ("kind", C.c_int32),
@@ -73,6 +99,7 @@ class EnvCfg(C.Structure):
         ("obs_ub", C.c_double * MAX_DO),
         ("env_act_noise_std", C.c_double * MAX_DA),
         ("env_act_noise_mean", C.c_double * MAX_DA),
+        ("wrap", StepWrappers),
     ]
 
 

@@ -29,6 +29,31 @@ int check_cfg(const sre_env_cfg *cfg) {
         for (int i = 0; i < k_do[cfg->kind]; i++)
             SRE_CHECK_ARG(std::isfinite(cfg->obs_lb[i]) && std::isfinite(cfg->obs_ub[i]) && cfg->obs_ub[i] > cfg->obs_lb[i],
                           SRE_E_ARG, "obs_norm bounds of observation %d are [%g, %g]", i, cfg->obs_lb[i], cfg->obs_ub[i]);
+    const sre_step_wrappers &w = cfg->wrap;
+    SRE_CHECK_ARG(w.act_delay >= 0 && w.act_delay <= SRE_MAX_DELAY, SRE_E_ARG, "act_delay %d outside [0, %d]", w.act_delay,
+                  SRE_MAX_DELAY);
+    SRE_CHECK_ARG(w.downsample >= 0 && w.downsample <= SRE_MAX_DOWN, SRE_E_ARG, "downsample %d outside [0, %d]",
+                  w.downsample, SRE_MAX_DOWN);
+    SRE_CHECK_ARG(w.vf_n >= 0 && w.vf_n <= SRE_MAX_VF && w.n_aug >= 0 && w.n_aug <= SRE_MAX_AUG, SRE_E_ARG,
+                  "vf_n %d / n_aug %d out of range", w.vf_n, w.n_aug);
+    SRE_CHECK_ARG((w.obs_keep_mask >> k_do[cfg->kind]) == 0 && w.obs_keep_mask >= 0, SRE_E_ARG,
+                  "obs_keep_mask 0x%x has bits beyond the %d observations", w.obs_keep_mask, k_do[cfg->kind]);
+    for (int i = 0; i < w.vf_n; i++)
+        SRE_CHECK_ARG(w.vf_pos[i] >= 0 && w.vf_pos[i] < k_ds[cfg->kind] && w.vf_vel[i] >= 0 && w.vf_vel[i] < k_do[cfg->kind],
+                      SRE_E_ARG, "velocity filter pair %d: state %d / observation %d", i, w.vf_pos[i], w.vf_vel[i]);
+    for (int i = 0; i < w.n_aug; i++)
+        SRE_CHECK_ARG(w.aug_param[i] >= 0 && w.aug_param[i] < k_dp[cfg->kind], SRE_E_ARG, "augmented parameter %d: index %d",
+                      i, w.aug_param[i]);
+    SRE_CHECK_ARG(!(cfg->obs_noise || cfg->obs_norm) || !(w.downsample > 1 || w.obs_keep_mask || w.vf_n || w.n_aug),
+                  SRE_E_UNSUPPORTED, "observation noise / normalisation cannot be combined with the fused observation wrappers");
+    return 0;
+}
+
+// the step-granular entry points do not carry wrapper state between launches
+int reject_step_wrappers(const sre_env_cfg *cfg, const char *what) {
+    const sre_step_wrappers &w = cfg->wrap;
+    SRE_CHECK_ARG(!(w.act_delay > 0 || w.downsample > 1 || w.obs_keep_mask != 0 || w.vf_n > 0 || w.n_aug > 0),
+                  SRE_E_UNSUPPORTED, "%s: cfg.wrap is only implemented by sre_rollout", what);
     return 0;
 }
 
@@ -306,6 +331,7 @@ int sre_reset(const sre_env_cfg *cfg, const void *params, const void *init, int 
               uint32_t episode, int64_t n, void *stream) {
     int e = check_cfg(cfg);
     if (e) return e;
+    if ((e = reject_step_wrappers(cfg, "sre_reset"))) return e;
     SRE_CHECK_ARG(init && state && hidden && curr_step && n >= 0, SRE_E_ARG, "NULL pointer or n < 0");
     // base.py:184-193: full state or an element of the init space
     SRE_CHECK_ARG(n_init_cols == k_ds[cfg->kind] || n_init_cols == k_dinit[cfg->kind], SRE_E_ARG,
@@ -322,6 +348,7 @@ int sre_step(const sre_env_cfg *cfg, const void *params, const void *act, void *
              uint64_t env_offset, uint32_t episode, int64_t n, void *stream) {
     int e = check_cfg(cfg);
     if (e) return e;
+    if ((e = reject_step_wrappers(cfg, "sre_step"))) return e;
     SRE_CHECK_ARG(act && state && hidden && curr_step && obs && rew && done && n >= 0, SRE_E_ARG,
                   "NULL pointer or n < 0");
     if (n == 0) return 0;
@@ -379,7 +406,13 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
                   (long long)io->n_envs, (long long)io->n_rows);
     const int kind = cfg->kind;
     KPolicy kp;
-    e = make_kpolicy(pol, k_do[kind], k_da[kind], kp);
+    // policy input width behind ObsPartialWrapper / StateAugmentationWrapper
+    int n_pol_in = k_do[kind];
+    if (cfg->wrap.obs_keep_mask) n_pol_in = __builtin_popcount((unsigned)cfg->wrap.obs_keep_mask);
+    n_pol_in += cfg->wrap.n_aug;
+    SRE_CHECK_ARG(!pol || pol->kind != SRE_POL_LINEAR || n_pol_in == k_do[kind], SRE_E_UNSUPPORTED,
+                  "the fused linear policy needs the full observation (got %d of %d entries)", n_pol_in, k_do[kind]);
+    e = make_kpolicy(pol, n_pol_in, k_da[kind], kp);
     if (e) return e;
     SRE_CHECK_ARG(!kp.cartpole_feats, SRE_E_UNSUPPORTED,
                   "cartpole_feats (the fork's 4-dim FNNPolicy input) is only available in sre_policy_forward");

@@ -21,6 +21,14 @@ template <typename R> struct KTask {
     int q_diag;  // Q and R are diagonal: 3*ds + 3*da flops instead of the dense form
 };
 
+#define SRE_MAX_POL_IN (SRE_MAX_DO + SRE_MAX_AUG)  // widest policy input with StateAugmentationWrapper
+template <typename R> struct KWrap {
+    int active, delay, delay_inner, delay_first, down, keep_mask, vf_n, n_aug, aug_fixed;
+    int vf_pos[SRE_MAX_VF], vf_vel[SRE_MAX_VF], aug_param[SRE_MAX_AUG];
+    R vf_b0, vf_b1, vf_a1, vf_zi;
+    R aug_nominal[SRE_MAX_AUG];
+};
+
 template <typename R> struct KCfg {
     int flags, wild_init, act_norm, obs_noise, has_init_box, obs_norm, env_act_noise;
     long long max_steps;  // <= 0: inf
@@ -31,6 +39,7 @@ template <typename R> struct KCfg {
     R obs_lb[SRE_MAX_DO], obs_span[SRE_MAX_DO];  // ObsNormWrapper: lower bound and (ub - lb)
     R an_std[SRE_MAX_DA], an_mean[SRE_MAX_DA];    // GaussianActNoiseWrapper
     double init_box_lo[SRE_MAX_DS], init_box_up[SRE_MAX_DS];
+    KWrap<R> wrap;
 };
 
 struct KDistr {

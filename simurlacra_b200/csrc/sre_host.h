@@ -88,9 +88,29 @@ template <typename R> inline void make_kcfg(const sre_env_cfg &c, KCfg<R> &k) {
         k.init_box_lo[i] = c.init_box_lo[i];
         k.init_box_up[i] = c.init_box_up[i];
     }
+    const sre_step_wrappers &w = c.wrap;
+    k.wrap.delay = w.act_delay;
+    k.wrap.delay_inner = w.act_delay_inner;
+    k.wrap.delay_first = w.delay_first;
+    k.wrap.down = w.downsample > 1 ? w.downsample : 0;
+    k.wrap.keep_mask = w.obs_keep_mask;
+    k.wrap.vf_n = w.vf_n;
+    k.wrap.n_aug = w.n_aug;
+    k.wrap.aug_fixed = w.aug_fixed;
+    for (int i = 0; i < SRE_MAX_VF; i++) {
+        k.wrap.vf_pos[i] = w.vf_pos[i];
+        k.wrap.vf_vel[i] = w.vf_vel[i];
+    }
+    k.wrap.vf_b0 = (R)w.vf_b0; k.wrap.vf_b1 = (R)w.vf_b1; k.wrap.vf_a1 = (R)w.vf_a1; k.wrap.vf_zi = (R)w.vf_zi;
+    for (int i = 0; i < SRE_MAX_AUG; i++) {
+        k.wrap.aug_param[i] = w.aug_param[i];
+        k.wrap.aug_nominal[i] = (R)w.aug_nominal[i];
+    }
+    k.wrap.active = (w.act_delay > 0 || w.downsample > 1 || w.obs_keep_mask != 0 || w.vf_n > 0 || w.n_aug > 0) ? 1 : 0;
 }
 
 int check_cfg(const sre_env_cfg *cfg);
+int reject_step_wrappers(const sre_env_cfg *cfg, const char *what);
 int make_kdistr(const sre_env_cfg *cfg, const sre_distr *distr, int n_distr, KDistr &kd);
 int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp);
 

@@ -117,6 +117,89 @@ template <int KIND, typename R> SRE_DEV float qbb_plate_ang(R arm_radius, R plat
     else return 0.f;
 }
 
+// ---- stateful step-path wrappers inside the persistent kernel (sre_step_wrappers, include/sre.h) --------------------
+// One wrapper state per environment lane, alive for the whole launch: the delay queue, the held action and step counter
+// of the downsampling, its observation ring, the velocity-filter memory, the augmented parameters.  Only the generic
+// body of the un-tiled policy variants carries it (WRAP below); the state lives in local memory, nothing of it touches
+// the specialised hot bodies.
+template <typename R, int DO, int DA> struct WrapState {
+    R dq[SRE_MAX_DELAY * DA];
+    R hold[DA];
+    R ob[SRE_MAX_DOWN * DO];
+    R vz[SRE_MAX_VF];
+    R aug[SRE_MAX_AUG];
+    int dq_head, cnt, ob_n, ob_head;
+};
+template <typename R, int DO, int DA> SRE_DEV void wrap_init(WrapState<R, DO, DA> &w) {
+    for (int i = 0; i < SRE_MAX_DELAY * DA; i++) w.dq[i] = (R)0;
+    for (int i = 0; i < DA; i++) w.hold[i] = (R)0;
+    for (int i = 0; i < SRE_MAX_VF; i++) w.vz[i] = (R)0;
+    for (int i = 0; i < SRE_MAX_AUG; i++) w.aug[i] = (R)0;
+    w.dq_head = w.cnt = w.ob_n = w.ob_head = 0;
+}
+// ActDelayWrapper._process_act (action_delay.py:102-110): append the action, pop the oldest
+template <typename R, int DO, int DA> SRE_DEV void wrap_delay(const KWrap<R> &k, WrapState<R, DO, DA> &w, R *act) {
+    for (int i = 0; i < DA; i++) {
+        const R old = w.dq[w.dq_head * DA + i];
+        w.dq[w.dq_head * DA + i] = act[i];
+        act[i] = old;
+    }
+    w.dq_head = (w.dq_head + 1 == k.delay) ? 0 : w.dq_head + 1;
+}
+// The observation path for ONE new observation of the lane (episode start or after a step): ObsVelFiltWrapper
+// (observation_velfilter.py:119-145; init_filter :107-117 at a reset), DownsamplingWrapper._process_obs
+// (downsampling.py:134-141; reset :118-131: the first observation is filtered with what the previous episode left in the
+// buffer and the result seeds the new one), ObsPartialWrapper (observation_partial.py:63-75), StateAugmentationWrapper
+// (state_augmentation.py:75-81).  Also resets the action-side state at an episode start.
+template <typename R, int DO, int DA, int DS>
+SRE_DEV int wrap_observe(const KWrap<R> &k, WrapState<R, DO, DA> &w, const R *state, const R *obs, bool reset, R *out) {
+    R v[DO];
+#pragma unroll
+    for (int i = 0; i < DO; i++) v[i] = obs[i];
+    if (reset) {
+        for (int i = 0; i < SRE_MAX_DELAY * DA; i++) w.dq[i] = (R)0;
+        w.dq_head = 0;
+        w.cnt = 0;
+    }
+    for (int j = 0; j < k.vf_n; j++) {
+        R x = (R)0;
+#pragma unroll
+        for (int i = 0; i < DS; i++)
+            if (i == k.vf_pos[j]) x = state[i];
+        if (reset) w.vz[j] = k.vf_zi * x;
+        const R y = k.vf_b0 * x + w.vz[j];
+        w.vz[j] = k.vf_b1 * x - k.vf_a1 * y;
+#pragma unroll
+        for (int i = 0; i < DO; i++)
+            if (i == k.vf_vel[j]) v[i] = y;
+    }
+    if (k.down > 1) {
+        if (w.ob_n < k.down) {
+            const int at = (w.ob_head + w.ob_n) % k.down;
+            for (int i = 0; i < DO; i++) w.ob[at * DO + i] = v[i];
+            w.ob_n++;
+        } else {
+            for (int i = 0; i < DO; i++) w.ob[w.ob_head * DO + i] = v[i];
+            w.ob_head = (w.ob_head + 1) % k.down;
+        }
+        for (int i = 0; i < DO; i++) {
+            R sum = w.ob[w.ob_head * DO + i];  // oldest first, like np.mean over the deque
+            for (int q = 1; q < w.ob_n; q++) sum += w.ob[((w.ob_head + q) % k.down) * DO + i];
+            v[i] = sum / (R)w.ob_n;
+        }
+        if (reset) {
+            for (int i = 0; i < DO; i++) w.ob[i] = v[i];
+            w.ob_head = 0;
+            w.ob_n = 1;
+        }
+    }
+    int n = 0;
+    for (int i = 0; i < DO; i++)
+        if (k.keep_mask == 0 || ((k.keep_mask >> i) & 1)) out[n++] = v[i];
+    for (int j = 0; j < k.n_aug; j++) out[n++] = k.aug_fixed ? k.aug_nominal[j] : w.aug[j];
+    return n;
+}
+
 // MODE (compile time) -- what the step body has to be able to do:
 //   SRE_MODE_GENERIC  everything decided at run time (records, observation noise / normalisation, action noises, dense
 //                     Q / R, FinalRewTask): the kernel of round 1
@@ -136,6 +219,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     using RC = Rec<KIND, R>;
     constexpr int DS = E::DS, DO = E::DO, DA = E::DA, DP = E::DP, NH = E::NH, W = RC::W;
     constexpr bool PLAIN = MODE != SRE_MODE_GENERIC;
+    constexpr bool WRAP = MODE == SRE_MODE_GENERIC && PV < 16;  // the bodies that can run the stateful step wrappers
+    constexpr int NIN = WRAP ? SRE_MAX_POL_IN : DO;
     // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
     using Fast = FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>;
     constexpr bool TC = PV >= SRE_PV_TC;
@@ -192,6 +277,16 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     bool first_episode = true;
     bool failed_ep = false;
     int status = 0;
+    // stateful step wrappers (only in the bodies that carry them; `wrapped` is launch-uniform)
+    const bool wrapped = WRAP && cfg.wrap.active;
+    WrapState<R, DO, DA> ws;
+    R wobs[NIN];  // the observation the policy sees (and the record keeps) when `wrapped`
+    int n_in = DO;
+    if (WRAP) {
+        if (wrapped) wrap_init(ws);
+#pragma unroll
+        for (int i = 0; i < NIN; i++) wobs[i] = (R)0;
+    }
     // statistics: accumulated per CTA in shared memory when an episode closes (rare), so that no statistics
     // registers stay live across the hot loop; one global atomic set per CTA at the end
     __shared__ double sm_stats[SRE_N_STATS];
@@ -245,6 +340,15 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
         if (mine) {
             D.set_params(cfg, dp);
+            if (WRAP && wrapped && live) {  // StateAugmentationWrapper: this episode's values of the selected parameters
+                for (int j = 0; j < cfg.wrap.n_aug; j++) {
+                    R v = (R)0;
+#pragma unroll
+                    for (int i = 0; i < DP; i++)
+                        if (i == cfg.wrap.aug_param[j]) v = dp[i];
+                    ws.aug[j] = v;
+                }
+            }
             if (live && first_episode && io.params_out) {
 #pragma unroll
                 for (int i = 0; i < DP; i++) static_cast<R *>(io.params_out)[n * DP + i] = dp[i];
@@ -373,6 +477,8 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
         if (!PLAIN && (stepping || closing) && cfg.obs_noise) add_obs_noise<DO, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, obs);
         if (!PLAIN && (stepping || closing) && cfg.obs_norm) apply_obs_norm<DO, R>(cfg, obs);
+        if (WRAP && wrapped && (stepping || closing))  // exactly one new observation per stepping / closing row
+            n_in = wrap_observe<R, DO, DA, DS>(cfg.wrap, ws, L.s, obs, t_ep == 0, wobs);
         // ---- policy (float32).  The tiled FNN is warp-cooperative, so it runs outside the per-lane branches ----
         R act[DA];
         if (PV == SRE_PV_ACTIONS) {
@@ -382,9 +488,9 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                              ? static_cast<const R *>(io.actions)[(row * N + n) * DA + i]
                              : (R)0;
         } else {
-            float of[DO], af[DA];
+            float of[NIN], af[DA];
 #pragma unroll
-            for (int i = 0; i < DO; i++) of[i] = (float)obs[i];
+            for (int i = 0; i < NIN; i++) of[i] = (float)((WRAP && wrapped) ? wobs[i] : (i < DO ? obs[i] : (R)0));
             if (TC) {
                 // CTA-cooperative (tcgen05), no CTA barrier inside.  Every 16 rows the CTA agrees on whether any of
                 // its lanes is still running (the exit has to be CTA-uniform: all four warps feed each MMA)
@@ -396,7 +502,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             else {
                 // parameter exploration: this lane's own parameter set, straight from global memory (L2-resident)
                 const float *wsrc = per_lane_w ? pol.weights + (valid ? n / pol.group_size : 0) * pol.n_weights : sm_w;
-                if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, wsrc, of, DO, af, DA);
+                if (PV == SRE_PV_GENERIC) fnn_generic_forward(pol, wsrc, of, (WRAP && wrapped) ? n_in : DO, af, DA);
                 else linear_forward<DO, DA>(pol, wsrc, of, af);
             }
             if (!PLAIN && pol.act_noise && stepping)
@@ -409,6 +515,22 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             R act_env[DA];
 #pragma unroll
             for (int i = 0; i < DA; i++) act_env[i] = act[i];
+            if (WRAP && wrapped) {
+                // DownsamplingWrapper._process_act (downsampling.py:143-151) and the outer ActDelayWrapper, in chain order
+                const KWrap<R> &kw = cfg.wrap;
+                if (kw.delay > 0 && !kw.delay_inner && kw.delay_first) wrap_delay(kw, ws, act_env);
+                if (kw.down > 1) {
+                    if (ws.cnt % kw.down == 0) {
+#pragma unroll
+                        for (int i = 0; i < DA; i++) ws.hold[i] = act_env[i];
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < DA; i++) act_env[i] = ws.hold[i];
+                    }
+                    ws.cnt++;
+                }
+                if (kw.delay > 0 && !kw.delay_inner && !kw.delay_first) wrap_delay(kw, ws, act_env);
+            }
             // GaussianActNoiseWrapper outside / inside ActNormWrapper (the recorded action stays the policy's)
             if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_OUTER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
@@ -419,6 +541,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 if (cfg.act_norm) act_env[i] = a_lo[i] + (act_env[i] + (R)1) * (a_up[i] - a_lo[i]) / (R)2;
             if (!PLAIN && cfg.env_act_noise == SRE_ENV_ACT_NOISE_INNER)
                 add_env_act_noise<DA, R>(cfg, io.seed, genv, episode, (uint32_t)t_ep, act_env);
+            if (WRAP && wrapped && cfg.wrap.delay > 0 && cfg.wrap.delay_inner) wrap_delay(cfg.wrap, ws, act_env);
 #pragma unroll
             for (int i = 0; i < DA; i++) {
                 if (m_isnan(act[i])) status |= SRE_ST_NAN_ACT;
@@ -437,7 +560,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             }
 #pragma unroll
             for (int i = 0; i < DO; i++) {
-                if (record) my_rec[RC::OFF_OBS + i] = obs[i];
+                if (record) my_rec[RC::OFF_OBS + i] = (WRAP && wrapped) ? (i < n_in ? wobs[i] : (R)0) : obs[i];
                 if (m_isnan(obs[i])) status |= SRE_ST_NAN_OBS;
             }
             if (record) {
@@ -464,7 +587,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
             // closing row (rollout.py:309-311): final observation / state, nothing else
             if (record) {
 #pragma unroll
-                for (int i = 0; i < DO; i++) my_rec[RC::OFF_OBS + i] = obs[i];
+                for (int i = 0; i < DO; i++) my_rec[RC::OFF_OBS + i] = (WRAP && wrapped) ? (i < n_in ? wobs[i] : (R)0) : obs[i];
 #pragma unroll
                 for (int i = 0; i < DS; i++) my_rec[RC::OFF_STATE + i] = L.s[i];
 #pragma unroll
@@ -575,7 +698,7 @@ static int launch_rollout_mode(const KCfg<R> &cfg, const KDistr &distr, const KP
     // where the resident CTAs of an SM still fit its shared memory
     const size_t slot_bytes = (size_t)threads * Lane<KIND, R>::NSLOT * sizeof(R);
     const char *noprep = getenv("SRE_NO_PREP");
-    io2.prep_slots = io_in.auto_reset && !(noprep && noprep[0] == '1') &&
+    io2.prep_slots = io_in.auto_reset && !(noprep && noprep[0] == '1') && !cfg.wrap.active &&
                      (smem + slot_bytes + 1024) * LaunchShape<R, PV>::MIN_BLOCKS <= 220 * 1024;
     if (io2.prep_slots) smem += slot_bytes;
     const KIO &io = io2;
@@ -622,7 +745,8 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
         return launch_rollout_pv<KIND, R, SRE_PV_LINEAR>(cfg, distr, pol, io, stream);
     }
     // FNN: the register-resident fast path needs [do, H, H, da] with tanh hidden and linear output
-    const bool two_hidden = pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
+    // the stateful step wrappers live in the generic body of the un-tiled variants
+    const bool two_hidden = !cfg.wrap.active && pol.n_layers == 3 && pol.sizes[0] == E::DO && pol.sizes[3] == E::DA &&
                             pol.sizes[1] == pol.sizes[2] && pol.hidden_nonlin == 0 && pol.output_nonlin == 0 &&
                             !pol.cartpole_feats;
     const int fast_threads = two_hidden && pol.sizes[1] == 64 && pol.precision != SRE_PREC_FP32 && sizeof(R) == 4

@@ -84,9 +84,12 @@ def make_task(kind: int, state_des=None, Q=None, R=None, rew_kind=None, min_rew=
 def make_cfg(kind: int, dt: float, max_steps: int = 0, dtype=torch.float32, simple_dynamics: bool = False,
              long_pole: bool = False, wild_init: int = 0, task: Optional[L.Task] = None, base_params=None,
              act_norm: bool = False, noise_std=None, noise_mean=None, init_box=None, flags: int = 0,
-             obs_norm=None, env_act_noise=None) -> L.EnvCfg:
+             obs_norm=None, env_act_noise=None, wrap: Optional[dict] = None) -> L.EnvCfg:
     """`obs_norm` = (lb, ub) of ObsNormWrapper; `env_act_noise` = (position, std, mean) of GaussianActNoiseWrapper with
-    position L.ENV_ACT_NOISE_OUTER (outside ActNormWrapper) or L.ENV_ACT_NOISE_INNER."""
+    position L.ENV_ACT_NOISE_OUTER (outside ActNormWrapper) or L.ENV_ACT_NOISE_INNER; `wrap` = the stateful step-path
+    wrappers of the persistent rollout (sre_step_wrappers): keys act_delay, act_delay_inner, delay_first, downsample,
+    obs_keep (indices kept by ObsPartialWrapper), velfilt = (pos state indices, vel obs indices, b0, b1, a1, zi),
+    augment = (parameter indices, nominal values, fixed)."""
     cfg = L.EnvCfg()
     cfg.kind = kind
     cfg.dtype = L.F64 if dtype == torch.float64 else L.F32
@@ -118,6 +121,25 @@ def make_cfg(kind: int, dt: float, max_steps: int = 0, dtype=torch.float32, simp
             cfg.env_act_noise_std[i] = v
         for i, v in enumerate(np.asarray(env_act_noise[2], dtype=np.float64).reshape(-1)):
             cfg.env_act_noise_mean[i] = v
+    if wrap:
+        w = cfg.wrap
+        w.act_delay = int(wrap.get("act_delay", 0))
+        w.act_delay_inner = int(bool(wrap.get("act_delay_inner", False)))
+        w.delay_first = int(bool(wrap.get("delay_first", False)))
+        w.downsample = int(wrap.get("downsample", 0))
+        if wrap.get("obs_keep") is not None:
+            w.obs_keep_mask = sum(1 << int(i) for i in wrap["obs_keep"])
+        if wrap.get("velfilt") is not None:
+            pos, vel, b0, b1, a1, zi = wrap["velfilt"]
+            w.vf_n = len(pos)
+            for i, (p_, v_) in enumerate(zip(pos, vel)):
+                w.vf_pos[i], w.vf_vel[i] = int(p_), int(v_)
+            w.vf_b0, w.vf_b1, w.vf_a1, w.vf_zi = float(b0), float(b1), float(a1), float(zi)
+        if wrap.get("augment") is not None:
+            idx, nominal, fixed = wrap["augment"]
+            w.n_aug, w.aug_fixed = len(idx), int(bool(fixed))
+            for i, (p_, v_) in enumerate(zip(idx, nominal)):
+                w.aug_param[i], w.aug_nominal[i] = int(p_), float(v_)
     if init_box is not None:
         cfg.has_init_box = 1
         for i, v in enumerate(np.asarray(init_box[0], dtype=np.float64).reshape(-1)):

@@ -20,6 +20,9 @@ class ActDelayWrapper(EnvWrapperAct):
         self._delay = delay
         self._act_queue = []
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        return True  # the persistent rollout kernel keeps this wrapper's state per lane (sampling/rollout.py::_compile_step_wrappers)
+
     def _ctor_kwargs(self) -> dict:
         return dict(delay=self._delay)
 

@@ -41,6 +41,17 @@ class ActNormWrapper(EnvWrapperAct):
         fusion.act_norm = True
         return True
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        from .action_delay import ActDelayWrapper
+        from .action_noise import GaussianActNoiseWrapper
+        from .downsampling import DownsamplingWrapper
+
+        # the persistent kernel also runs an action delay (in env units) and the downsampling hold below the normalisation
+        if any(w._alters_act and type(w) not in (GaussianActNoiseWrapper, ActDelayWrapper, DownsamplingWrapper) for w in below):
+            return False
+        fusion.act_norm = True
+        return True
+
     def _process_act(self, act):
         lb, ub = self.wrapped_env.act_space.bounds
         if isinstance(act, torch.Tensor):

@@ -170,6 +170,11 @@ class EnvWrapper(Env):
         """Record this wrapper in `fusion` if the kernels implement it; return False if it has to run on the arrays."""
         return True  # pure delegation needs nothing
 
+    def _fuse_rollout(self, fusion: Fusion, below: list) -> bool:
+        """The same question for the persistent rollout kernel, which also runs the stateful step wrappers
+        (sampling/rollout.py::_compile_step_wrappers decides about their order); default: what `_fuse` says."""
+        return self._fuse(fusion, any(b._alters_act for b in below), any(b._alters_obs for b in below))
+
     def _below(self):
         env = self._wrapped_env
         while isinstance(env, EnvWrapper):

@@ -30,6 +30,9 @@ class DownsamplingWrapper(EnvWrapperAct, EnvWrapperObs):
         self._obs_buffer = deque([] if init_obs is None else [np.array(init_obs, copy=True)], maxlen=factor)
         self._obs_filter_fcn = obs_filter_fcn
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        return True  # the persistent rollout kernel keeps this wrapper's state per lane (sampling/rollout.py::_compile_step_wrappers)
+
     def _ctor_kwargs(self) -> dict:
         return dict(factor=self._factor, obs_filter_fcn=self._obs_filter_fcn)
 

@@ -34,6 +34,9 @@ class ObsPartialWrapper(EnvWrapperObs):
         self.keep_mask = mask if keep_selected else np.logical_not(mask)
         self._keep_idx = None
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        return True  # the persistent rollout kernel keeps this wrapper's state per lane (sampling/rollout.py::_compile_step_wrappers)
+
     def _ctor_kwargs(self) -> dict:
         return dict(self._ctor)
 

@@ -54,6 +54,9 @@ class ObsVelFiltWrapper(EnvWrapperObs):
         self._a = np.concatenate([self.a, np.zeros(n - len(self.a))]).astype(np.float64) / float(self.a[0])
         self.z = np.zeros((n - 1, int(self.mask_pos.sum())), dtype=np.float32)
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        return True  # the persistent rollout kernel keeps this wrapper's state per lane (sampling/rollout.py::_compile_step_wrappers)
+
     def _ctor_kwargs(self) -> dict:
         return dict(self._ctor)
 

@@ -31,6 +31,9 @@ class StateAugmentationWrapper(EnvWrapper):
         self._nominal = np.array([nominal[k] for k in self._params], dtype=np.float64)
         self.fixed = fixed
 
+    def _fuse_rollout(self, fusion, below) -> bool:
+        return True  # the persistent rollout kernel keeps this wrapper's state per lane (sampling/rollout.py::_compile_step_wrappers)
+
     def _ctor_kwargs(self) -> dict:
         return dict(domain_param=self._params, fixed=self.fixed)
 

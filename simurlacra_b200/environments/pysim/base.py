@@ -34,6 +34,7 @@ class Fusion:
         self.noise_mean = None
         self.obs_norm = None        # (lb, ub) of an ObsNormWrapper
         self.env_act_noise = None   # (position, std, mean) of a GaussianActNoiseWrapper
+        self.wrap = None            # dict of the stateful step wrappers the persistent rollout kernel runs (engine.make_cfg)
 
 
 class SimPyEnv(SimEnv):
@@ -208,7 +209,7 @@ class SimPyEnv(SimEnv):
                           simple_dynamics=bool(self._flags & L.F_SIMPLE_DYN), wild_init=self._wild_init, task=task,
                           base_params=self.base_param_vector(), act_norm=f.act_norm, noise_std=f.noise_std,
                           noise_mean=f.noise_mean, init_box=init_box, flags=self._flags & ~L.F_SIMPLE_DYN,
-                          obs_norm=f.obs_norm, env_act_noise=f.env_act_noise)
+                          obs_norm=f.obs_norm, env_act_noise=f.env_act_noise, wrap=f.wrap)
 
     def _alloc(self):
         if self._state is None:

@@ -166,7 +166,7 @@ class ParallelRolloutSampler(SamplerBase):
                 res = self._launch(a, b, desc, None if init_all is None else init_all[a:b].contiguous(),
                                    None if params_all is None else params_all[a:b].contiguous(), stats=stats)
                 self._check_status(res)
-                ros.extend(sequences_from_records(self.env, sim, res, sim.dt, self.data_format))
+                ros.extend(sequences_from_records(self.env, sim, res, sim.dt, self.data_format, obs_layout=cc.obs_layout))
         else:
             if init_states is not None:
                 raise NotImplementedError  # like the reference (parallel_rollout_sampler.py:319-320)
@@ -192,7 +192,8 @@ class ParallelRolloutSampler(SamplerBase):
             for start, res in results:
                 ids = np.arange(max(lo, start), min(hi, start + chunk)) - start
                 if len(ids):
-                    ros.extend(sequences_from_records(self.env, sim, res, sim.dt, self.data_format, env_ids=ids))
+                    ros.extend(sequences_from_records(self.env, sim, res, sim.dt, self.data_format, env_ids=ids,
+                                                      obs_layout=cc.obs_layout))
                     # statistics of the kept rollouts only, from the kernel's per-lane results (no per-rollout pass)
                     r = res["ret"].double().cpu().numpy()[ids]
                     ln = res["length"].cpu().numpy()[ids].astype(np.float64)

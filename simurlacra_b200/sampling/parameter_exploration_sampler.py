@@ -226,7 +226,7 @@ class ParameterExplorationSampler:
             full = torch.full((P,), float("nan"), dtype=torch.float64, device=mean_ret.device)
             full[lo:hi] = mean_ret
             mean_ret = full
-        ros = sequences_from_records(self.env, sim, res, float(sim.dt)) if return_rollouts else []
+        ros = sequences_from_records(self.env, sim, res, float(sim.dt), obs_layout=cc.obs_layout) if return_rollouts else []
         samples = [ParameterSample(params=param_sets[p],
                                    rollouts=ros[(p - lo) * R:(p - lo + 1) * R] if return_rollouts and lo <= p < hi else [])
                    for p in range(P)]

@@ -39,8 +39,89 @@ HIDDEN_FIELD = {L.QCP: "th_ddot", L.QBB: "plate_angs"}  # name of the hidden-sta
 class CompiledChain:
     """An env chain reduced to what the rollout kernel needs."""
 
-    def __init__(self, sim: SimPyEnv, fusion: Fusion, live_randomizer, buffer_wrappers):
+    def __init__(self, sim: SimPyEnv, fusion: Fusion, live_randomizer, buffer_wrappers, obs_layout=None):
         self.sim, self.fusion, self.live_randomizer, self.buffer_wrappers = sim, fusion, live_randomizer, buffer_wrappers
+        # with fused ObsPartial / StateAugmentation wrappers: (number of observation entries the record holds,
+        # parameter indices, nominal values, fixed) -- how the policy's observation is rebuilt from a record
+        self.obs_layout = obs_layout
+
+
+def _compile_step_wrappers(sim: SimPyEnv, chain: list, fusion: Fusion):
+    """The stateful / shape-changing step wrappers of `chain` (outermost first) as the `wrap` dict of engine.make_cfg, for
+    the orders the persistent kernel implements (include/sre.h, sre_step_wrappers); False if this chain has to step.
+    Observation side, walked from the innermost wrapper outwards with the provenance of every entry."""
+    from scipy import signal
+
+    from ..environment_wrappers.action_delay import ActDelayWrapper
+    from ..environment_wrappers.action_noise import GaussianActNoiseWrapper
+    from ..environment_wrappers.action_normalization import ActNormWrapper
+    from ..environment_wrappers.downsampling import DownsamplingWrapper
+    from ..environment_wrappers.observation_partial import ObsPartialWrapper
+    from ..environment_wrappers.observation_velfilter import ObsVelFiltWrapper
+    from ..environment_wrappers.state_augmentation import StateAugmentationWrapper
+
+    kinds = (ActDelayWrapper, DownsamplingWrapper, ObsPartialWrapper, ObsVelFiltWrapper, StateAugmentationWrapper)
+    sw = [w for w in chain if isinstance(w, kinds)]
+    if not sw:
+        return None, None
+    if len({type(w) for w in sw}) != len(sw) or fusion.noise_std is not None or fusion.obs_norm is not None:
+        return False, None  # two of a kind, or observation noise / normalisation whose place in the order matters
+    depth = {type(w): i for i, w in enumerate(chain)}  # larger = closer to the simulation
+    d_obs, wrap = sim._dims["do"], {}
+    delay, down = depth.get(ActDelayWrapper), depth.get(DownsamplingWrapper)
+    norm = depth.get(ActNormWrapper)
+    if (delay is not None or down is not None) and any(isinstance(w, GaussianActNoiseWrapper) for w in chain):
+        return False, None
+    if delay is not None:
+        w = chain[delay]
+        d = w._delay
+        if isinstance(d, np.ndarray) and d.size != 1:
+            return False, None  # one delay per env: host path
+        d = int(w.delay)
+        if d > L.MAX_DELAY:
+            return False, None
+        inner = norm is not None and delay > norm
+        if inner and down is not None and down > delay:
+            return False, None  # hold below an inner delay: the kernel holds before the de-normalisation
+        wrap.update(act_delay=d, act_delay_inner=inner, delay_first=(down is not None and delay < down))
+    if down is not None:
+        w = chain[down]
+        if w._obs_filter_fcn is not None or not 1 <= int(w.factor) <= L.MAX_DOWN:
+            return False, None
+        wrap["downsample"] = int(w.factor)
+    src, seen_down = [("o", i) for i in range(d_obs)], False
+    for w in [w for w in chain[::-1] if isinstance(w, kinds)]:
+        if isinstance(w, ObsVelFiltWrapper):
+            if seen_down or len(w._b) != 2 or int(w.mask_pos.sum()) > L.MAX_VF or len(w.mask_vel) != len(src):
+                return False, None  # filter above the averaging, or not first order
+            vel = [src[i] for i in np.flatnonzero(w.mask_vel)]
+            if any(k != "o" for k, *_ in vel):
+                return False, None
+            wrap["velfilt"] = (list(np.flatnonzero(w.mask_pos)), [v[1] for v in vel], w._b[0], w._b[1], w._a[1],
+                               float(signal.lfilter_zi(w.b, w.a)[0]))
+        elif isinstance(w, DownsamplingWrapper):
+            if any(k == "a" for k, *_ in src):
+                return False, None  # averaging over appended parameters carries the last episode's values
+            seen_down = True
+        elif isinstance(w, ObsPartialWrapper):
+            if len(w.keep_mask) != len(src):
+                return False, None
+            src = [src[i] for i in np.flatnonzero(w.keep_mask)]
+        elif isinstance(w, StateAugmentationWrapper):
+            names = list(sim._param_names)
+            if any(k not in names for k in w._params):
+                return False, None
+            src = src + [("a", names.index(k), float(v), bool(w.fixed)) for k, v in zip(w._params, w._nominal)]
+    obs_part = [e[1] for e in src if e[0] == "o"]
+    aug = [e for e in src if e[0] == "a"]
+    if len(aug) > L.MAX_AUG or not obs_part and not aug:
+        return False, None
+    if obs_part != list(range(d_obs)):
+        wrap["obs_keep"] = obs_part
+    if aug:
+        wrap["augment"] = ([e[1] for e in aug], [e[2] for e in aug], aug[0][3])
+    layout = (len(obs_part), [e[1] for e in aug], [e[2] for e in aug], bool(aug and aug[0][3]))
+    return wrap, layout
 
 
 def compile_chain(env: Env) -> Optional[CompiledChain]:
@@ -52,7 +133,7 @@ def compile_chain(env: Env) -> Optional[CompiledChain]:
     chain = [e for e in all_envs(env) if isinstance(e, EnvWrapper)]
     for i, w in enumerate(chain):
         below = chain[i + 1:]
-        if not w._fuse(fusion, any(b._alters_act for b in below), any(b._alters_obs for b in below)):
+        if not w._fuse_rollout(fusion, below):
             return None
         if isinstance(w, DomainRandWrapperLive):
             if live is not None:
@@ -62,7 +143,11 @@ def compile_chain(env: Env) -> Optional[CompiledChain]:
             buffers.append(w)
     if sim._custom_init_space and type(sim.init_space).__name__ != "BoxSpace":
         return None
-    return CompiledChain(sim, fusion, live, buffers)
+    wrap, layout = _compile_step_wrappers(sim, chain, fusion)
+    if wrap is False:
+        return None
+    fusion.wrap = wrap
+    return CompiledChain(sim, fusion, live, buffers, layout)
 
 
 def _rollout_info(env: Env, sim, params_row: Optional[np.ndarray]) -> dict:
@@ -136,7 +221,7 @@ class LazyRolloutInfo(dict):
 
 
 def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_format: str = "numpy",
-                           env_ids: Optional[np.ndarray] = None) -> List[StepSequence]:
+                           env_ids: Optional[np.ndarray] = None, obs_layout=None) -> List[StepSequence]:
     """Cut the first episode of every lane out of the kernel's time-major record buffer (engine extension).
     'torch': every field of every StepSequence is a strided VIEW of the [T, N, W] device buffer (zero copy);
     'numpy': the used part of the buffer crosses to the host in ONE copy and the fields are views of that array.
@@ -156,6 +241,13 @@ def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_f
         time_all = torch.arange(t_max + 1, dtype=torch.get_default_dtype()) * dt
     o0, a0, p0, r0, s0, h0 = lay["obs"], lay["act"], lay["act_app"], lay["rew"], lay["state"], lay["hidden"]
     do, da, ds, nh = d["do"], d["da"], d["ds"], d["nh"]
+    aug_cols = None
+    if obs_layout is not None:  # fused ObsPartial / StateAugmentation: the record holds the kept entries; parameters are appended
+        do, aug_idx, aug_nom, aug_fixed = obs_layout
+        if aug_idx:
+            prm = res["params"][:, aug_idx] if not aug_fixed else torch.as_tensor(aug_nom, dtype=res["params"].dtype,
+                                                                                 device=res["params"].device).expand(n, -1)
+            aug_cols = prm.double().cpu().numpy() if data_format == "numpy" else prm.to(res["traj"].dtype)
     flags_last = res["row_flag"][:t_max].cpu().numpy()
     params = res["params"].double().cpu().numpy()
     names = sim._param_names if isinstance(sim, SimPyEnv) else ()
@@ -174,6 +266,10 @@ def sequences_from_records(env: Env, sim: SimPyEnv, res: dict, dt: float, data_f
                       actions_applied=col[:ln, p0:p0 + da], states=col[:ln + 1, s0:s0 + ds])
         if nh:
             fields[hname] = col[:ln + 1, h0] if nh == 1 else col[:ln + 1, h0:h0 + nh]
+        if aug_cols is not None:
+            o = fields["observations"]
+            fields["observations"] = (np.concatenate((o, np.broadcast_to(aug_cols[i], (ln + 1, aug_cols.shape[1]))), axis=1)
+                                      if data_format == "numpy" else torch.cat((o, aug_cols[i].expand(ln + 1, -1)), dim=1))
         ro = StepSequence.from_views(fields, ln, time_all[:ln + 1], LazyRolloutInfo(base_info, params[i], names, wrappers),
                                      True, data_format)
         ro.env_done = bool(flags_last[ln - 1, i] == L.ROW_DONE)  # False if the row budget (not the env) ended the episode
@@ -238,7 +334,7 @@ def _fused_rollout(env, cc: CompiledChain, desc, max_steps, reset_kwargs, stop_o
         first = res["params"][0].double().cpu().numpy()
         for i, k in enumerate(sim._param_names):
             sim._domain_param[k] = float(first[i])
-    return sequences_from_records(env, sim, res, sim.dt, data_format)
+    return sequences_from_records(env, sim, res, sim.dt, data_format, obs_layout=cc.obs_layout)
 
 
 def _state_copy(env):

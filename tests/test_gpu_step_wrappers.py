@@ -4,7 +4,8 @@ DownsamplingWrapper, ObsPartialWrapper, ObsVelFiltWrapper, StateAugmentationWrap
 (pyrado/environment_wrappers/action_delay.py, downsampling.py, observation_partial.py, observation_velfilter.py,
 state_augmentation.py) around QQubeSwingUpSim stepping on the step kernels, against trajectories of the UNMODIFIED
 reference wrappers (tests/golden/wrappers_reference.npz, made by `oracle/gen_golden.py wrappers`): single env in fp64
-like the reference, a float32 batch with per-env data, and through rollout() / ParallelRolloutSampler.
+like the reference, a float32 batch with per-env data, through rollout() / ParallelRolloutSampler, and -- the fused path
+-- inside the persistent rollout kernel (one wrapper state per lane, sre_step_wrappers) against the same trajectories.
 """
 import numpy as np
 import pytest
@@ -46,7 +47,7 @@ def test_single_env_matches_reference(name):
     env = CASES[name](QQubeSwingUpSim(dt=1 / 250.0, max_steps=60))
     np.testing.assert_allclose(env.obs_space.bound_lo, g[name + "_obs_lo"], rtol=1e-12)
     np.testing.assert_allclose(env.obs_space.bound_up, g[name + "_obs_up"], rtol=1e-12)
-    assert compile_chain(env) is None  # these run between step-kernel launches
+    assert compile_chain(env).fusion.wrap  # env.step runs them between step launches; rollouts fuse them (below)
     for episode in range(2):  # the second reset starts from clean wrapper state (queue, counter, filter)
         obs = [env.reset(init_state=g["init_state"].copy(), domain_param=dict(dp))]
         states, rews = [env.state], []
@@ -117,12 +118,65 @@ def test_per_env_data_in_a_batch():
     assert float(o[:, 4:].abs().max()) < 1e-5 and vf.z.shape == (1, n, 2)
 
 
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-9), (torch.float32, 2e-3)])
+def test_fused_in_the_persistent_kernel_matches_reference(name, dtype, tol):
+    """The whole horizon in ONE sre_rollout launch with the wrapper state per lane (injected golden actions): the
+    recorded observations are the wrapper's, states and rewards follow the reference."""
+    import simurlacra_b200.engine as E
+    from simurlacra_b200 import _lib as L
+
+    g = golden("wrappers_reference")
+    dp, act, T = _inputs(g, name)
+    n = 5
+    env = CASES[name](QQubeSwingUpSim(dt=1 / 250.0, max_steps=60, num_envs=n, dtype=dtype))
+    env.domain_param = dict(dp)
+    cc = compile_chain(env)
+    assert cc is not None and cc.fusion.wrap
+    sim = cc.sim
+    cfg = sim._make_cfg(cc.fusion)
+    dev = sim.device
+    init = torch.as_tensor(np.tile(g["init_state"], (n, 1)), dtype=dtype, device=dev)
+    acts = torch.as_tensor(np.tile(act[:T, None, :], (1, n, 1)), dtype=dtype, device=dev).contiguous()
+    res = E.rollout(cfg, E.make_policy(L.POL_ACTIONS), n, T + 1, device=dev, init=init, actions=acts, seed=3)
+    assert res["length"].tolist() == [T] * n
+    n_rec, aug_idx, aug_nom, aug_fixed = cc.obs_layout
+    obs = res["obs"][: T + 1, :, :n_rec].double().cpu().numpy()
+    ref = g[name + "_obs"][: T + 1]
+    for i in range(n):
+        np.testing.assert_allclose(obs[:, i], ref[:, :n_rec], rtol=tol, atol=tol)
+        np.testing.assert_allclose(res["state"][: T + 1, i].double().cpu().numpy(), g[name + "_states"][: T + 1], rtol=tol, atol=tol)
+        np.testing.assert_allclose(res["rew"][:T, i].double().cpu().numpy(), g[name + "_rews"][:T], rtol=tol, atol=tol)
+    if aug_idx:  # the appended parameters are rebuilt from the lane's parameter row
+        prm = res["params"][:, aug_idx].double().cpu().numpy() if not aug_fixed else np.tile(aug_nom, (n, 1))
+        np.testing.assert_allclose(prm, np.tile(ref[0, n_rec:], (n, 1)), rtol=1e-6)
+
+
+@pytest.mark.parametrize("name", list(CASES) + ["down_delay_partial"])
+def test_fused_rollout_equals_the_stepping_loop(name):
+    """rollout() with a fused FNN policy: the persistent kernel (wrappers fused) against the reference's loop over
+    env.step with the wrappers applied between step launches (record_dts=True forces it), single env in fp64."""
+    make = CASES.get(name) or (lambda e: ObsPartialWrapper(DownsamplingWrapper(ActNormWrapper(ActDelayWrapper(e, delay=2)),
+                                                                               factor=3), mask=[0, 1, 0, 0, 0, 0]))
+    env = make(QQubeSwingUpSim(dt=1 / 250.0, max_steps=40))
+    torch.manual_seed(1)
+    pol = FNNPolicy(env.spec, hidden_sizes=[12, 12], hidden_nonlin=torch.tanh)
+    assert compile_chain(env) is not None
+    fused = rollout(env, pol, seed=5, reset_kwargs=dict(init_state=np.array([0.1, -0.2, 0.3, 0.1])))
+    env2 = make(QQubeSwingUpSim(dt=1 / 250.0, max_steps=40))
+    loop = rollout(env2, pol, seed=5, record_dts=True, reset_kwargs=dict(init_state=np.array([0.1, -0.2, 0.3, 0.1])))
+    assert len(fused) == len(loop) and fused.observations.shape == loop.observations.shape
+    np.testing.assert_allclose(fused.observations, loop.observations, rtol=1e-5, atol=1e-5)  # float32 policy on both sides
+    np.testing.assert_allclose(fused.states, loop.states, rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(fused.actions, loop.actions, rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(fused.rewards, loop.rewards, rtol=1e-5, atol=1e-5)
+
+
 def test_through_rollout_and_sampler():
-    """The chains are not fusable into the persistent kernel: rollout() and the sampler take the stepping path and
-    still hand out StepSequences with the wrapper's observation width; delayed actions show up in actions_applied...
-    (the recorded action stays the policy's, like the reference)."""
+    """rollout() and the sampler hand out StepSequences with the wrapper's observation width (fused into the persistent
+    kernel); the recorded action stays the policy's, like the reference."""
     env = ObsPartialWrapper(ActNormWrapper(QQubeSwingUpSim(dt=1 / 250.0, max_steps=25)), idcs=["theta_dot", "alpha_dot"])
-    assert compile_chain(env) is None and env.obs_space.flat_dim == 4
+    assert compile_chain(env) is not None and env.obs_space.flat_dim == 4
     torch.manual_seed(0)
     pol = FNNPolicy(env.spec, hidden_sizes=[8], hidden_nonlin=torch.tanh)
     ro = rollout(env, pol, seed=0)
