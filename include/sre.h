@@ -281,6 +281,13 @@ typedef struct sre_rollout_io {
     void *params_out;         /* real [N, dp] parameters of the lane's first episode */
     double *stats;            /* [SRE_N_STATS] accumulated with atomics; caller initialises (sre_stats_init) */
     int32_t *status;          /* [N] SRE_ST_* bits */
+    /* Placement of this launch's lanes inside a WIDER record buffer: `traj` is real [T, traj_env_stride, W] and
+     * `row_flag` [T, traj_env_stride], lane n writes column traj_env_offset + n.  0 / 0: the buffers are [T, N, ...].
+     * This is how a rank writes its shard of the rollouts straight into the learner's buffer over NVLink (the pointers
+     * may be peer-mapped device memory): the gather of ParallelRolloutSampler's results overlaps the simulation tile by
+     * tile instead of following it as a collective. */
+    int64_t traj_env_stride;
+    int64_t traj_env_offset;
 } sre_rollout_io;
 
 /* ---- introspection (host only) ---------------------------------------------------------------------- */

@@ -161,6 +161,8 @@ class RolloutIO(C.Structure):
         ("params_out", C.c_void_p),
         ("stats", C.c_void_p),
         ("status", C.c_void_p),
+        ("traj_env_stride", C.c_int64),
+        ("traj_env_offset", C.c_int64),
     ]
 
 

@@ -426,6 +426,10 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
     if (io->init)
         SRE_CHECK_ARG(io->n_init_cols == k_ds[kind] || io->n_init_cols == k_dinit[kind], SRE_E_ARG,
                       "init has %d columns, expected %d or %d", io->n_init_cols, k_ds[kind], k_dinit[kind]);
+    SRE_CHECK_ARG(io->traj_env_stride == 0 ||
+                      (io->traj_env_offset >= 0 && io->traj_env_offset + io->n_envs <= io->traj_env_stride),
+                  SRE_E_ARG, "lanes [%lld, %lld) do not fit a record buffer of %lld columns", (long long)io->traj_env_offset,
+                  (long long)(io->traj_env_offset + io->n_envs), (long long)io->traj_env_stride);
     if (io->n_envs == 0) return 0;
     KIO k;
     memset(&k, 0, sizeof k);
@@ -433,6 +437,8 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
     k.episode = io->episode; k.stop_on_done = io->stop_on_done; k.auto_reset = io->auto_reset;
     k.params = io->params; k.init = io->init; k.actions = io->actions; k.n_init_cols = io->n_init_cols;
     k.traj = io->traj; k.row_flag = io->row_flag; k.ret = io->ret; k.length = io->length;
+    k.traj_stride = io->traj_env_stride > 0 ? io->traj_env_stride : io->n_envs;
+    k.traj_off = io->traj_env_stride > 0 ? io->traj_env_offset : 0;
     k.params_out = io->params_out; k.stats = io->stats; k.status = io->status;
     k.idle_policy = (pol->kind == SRE_POL_IDLE);
     cudaStream_t s = (cudaStream_t)stream;

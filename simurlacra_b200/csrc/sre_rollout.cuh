@@ -33,6 +33,7 @@ struct KIO {
     const void *params, *init, *actions;
     int n_init_cols;
     void *traj;
+    long long traj_stride, traj_off;  // record / flag buffers are [T, traj_stride, ...], lane n writes column traj_off + n
     unsigned char *row_flag;
     void *ret;
     int *length;
@@ -261,7 +262,9 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     const bool valid = n < N;
     const uint64_t genv = io.env_offset + (uint64_t)n;
     const int n_valid_lanes = (int)min((long long)32, max((long long)0, N - warp_env0));
-    const bool vec_ok = ((N * W * (long long)sizeof(R)) % 16 == 0) && ((reinterpret_cast<size_t>(io.traj) % 16) == 0);
+    const long long NS = io.traj_stride, NO = io.traj_off;
+    const bool vec_ok = ((NS * W * (long long)sizeof(R)) % 16 == 0) && ((NO * W * (long long)sizeof(R)) % 16 == 0) &&
+                        ((reinterpret_cast<size_t>(io.traj) % 16) == 0);
     const bool record = MODE == SRE_MODE_GENERIC ? io.traj != nullptr : MODE == SRE_MODE_PLAIN_REC;
     const bool want_flag = MODE == SRE_MODE_GENERIC ? io.row_flag != nullptr : MODE == SRE_MODE_PLAIN_REC;
 
@@ -635,7 +638,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
         }
 
         if (record) {
-            R *const gdst = static_cast<R *>(io.traj) + (row * N + warp_env0) * W;
+            R *const gdst = static_cast<R *>(io.traj) + (row * NS + NO + warp_env0) * W;
             const unsigned tile_bytes = (unsigned)(n_valid_lanes * W * sizeof(R));
             if (n_bufs == 2 && (tile_bytes & 15u) == 0u) {
                 fence_async_smem();
@@ -647,7 +650,7 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 __syncwarp();
             }
         }
-        if (want_flag && valid) io.row_flag[row * N + n] = flag;
+        if (want_flag && valid) io.row_flag[row * NS + NO + n] = flag;
         if (!TC && !record && !want_flag) {
             // early exit accounting: the warp leaves when every lane is idle
             if (__ballot_sync(0xffffffffu, lane_state != IDLE) == 0u) break;
@@ -688,7 +691,8 @@ static int launch_rollout_mode(const KCfg<R> &cfg, const KDistr &distr, const KP
     // (SRE_NO_BULK=1: the LDS / STG loop, for A/B measurements).  Measured: C4 (QBB, 256-thread CTAs) 1.78e10 -> 2.01e10
     // env-steps/s; the tensor-core variants (128-thread CTAs, four per SM) lose 3 % to the fence + wait and keep the loop.
     const char *nobulk = getenv("SRE_NO_BULK");
-    io2.stage_bufs = (PV < SRE_PV_TC && io_in.traj && ((size_t)io_in.n_envs * W * sizeof(R)) % 16 == 0 && (32 * W * sizeof(R)) % 16 == 0 &&
+    io2.stage_bufs = (PV < SRE_PV_TC && io_in.traj && ((size_t)io_in.traj_stride * W * sizeof(R)) % 16 == 0 &&
+                      ((size_t)io_in.traj_off * W * sizeof(R)) % 16 == 0 && (32 * W * sizeof(R)) % 16 == 0 &&
                       reinterpret_cast<size_t>(io_in.traj) % 16 == 0 && !(nobulk && nobulk[0] == '1'))
                          ? 2 : 1;
     size_t smem = (size_t)pol.smem_floats * sizeof(float) + io2.stage_bufs * tile_bytes;

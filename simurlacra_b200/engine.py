@@ -309,8 +309,11 @@ def policy_forward(pol: L.Policy, obs: torch.Tensor, n_act: int) -> torch.Tensor
 def rollout(cfg, pol: L.Policy, n_envs: int, n_rows: int, *, device, params=None, distr=None, init=None, actions=None,
             seed: int = 0, env_offset: int = 0, episode: int = 0, stop_on_done: bool = True, auto_reset: bool = False,
             record: bool = True, want_stats: bool = True, traj: Optional[torch.Tensor] = None,
-            row_flag: Optional[torch.Tensor] = None) -> dict:
-    """One launch of the persistent-horizon kernel. Returns device tensors (views into `traj` for the fields)."""
+            row_flag: Optional[torch.Tensor] = None, traj_env_offset: Optional[int] = None) -> dict:
+    """One launch of the persistent-horizon kernel. Returns device tensors (views into `traj` for the fields).
+    `traj_env_offset`: `traj` [T, M, W] / `row_flag` [T, M] are WIDER than this launch (M >= offset + n_envs, e.g. the
+    learner's buffer for all ranks, possibly peer-mapped); lane n writes column offset + n and the returned field views
+    are the launch's own columns."""
     dt_, d = cfg_dtype(cfg), dims(cfg.kind)
     lay = record_layout(cfg.kind)
     io = L.RolloutIO()
@@ -330,6 +333,11 @@ def rollout(cfg, pol: L.Policy, n_envs: int, n_rows: int, *, device, params=None
         if row_flag is None:
             row_flag = torch.empty(n_rows, n_envs, dtype=torch.uint8, device=device)
         io.traj, io.row_flag = _ptr(_chk(traj, dt_, "traj")), _ptr(_chk(row_flag, torch.uint8, "row_flag"))
+        if traj_env_offset is not None:
+            if traj.shape[1] != row_flag.shape[1] or traj_env_offset < 0 or traj_env_offset + n_envs > traj.shape[1]:
+                raise ValueError("traj / row_flag do not hold columns [offset, offset + n_envs)")
+            io.traj_env_stride, io.traj_env_offset = traj.shape[1], int(traj_env_offset)
+            traj, row_flag = traj[:, traj_env_offset: traj_env_offset + n_envs], row_flag[:, traj_env_offset: traj_env_offset + n_envs]
         res["traj"], res["row_flag"] = traj, row_flag
         res["obs"] = traj[..., lay["obs"]: lay["obs"] + d["do"]]
         res["act"] = traj[..., lay["act"]: lay["act"] + d["da"]]

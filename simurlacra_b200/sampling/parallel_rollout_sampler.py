@@ -248,12 +248,15 @@ class ParallelRolloutSampler(SamplerBase):
 
     # ------------------------------------------------------------------ engine extension: no host round trip
     def sample_batch(self, num_envs: int, *, auto_reset: bool = True, record: bool = False, eval: bool = True,
-                     traj: Optional[torch.Tensor] = None, row_flag: Optional[torch.Tensor] = None) -> dict:
+                     traj: Optional[torch.Tensor] = None, row_flag: Optional[torch.Tensor] = None,
+                     gather: Optional["sharding.RecordGather"] = None) -> dict:
         """
         One launch for `num_envs` lanes on this rank, results left ON THE DEVICE: returns / lengths / parameters of
         each lane's first episode, the all-reduced statistics vector and (with `record`) the time-major record buffer.
         With `auto_reset` every lane keeps starting new episodes until the horizon is used up (`min_steps`-style
         sampling: exactly `num_envs * max_steps` steps).  This is the call the benchmark times.
+        With `gather` (a `sharding.RecordGather` over num_envs * world_size rollouts) the records of all ranks are written
+        straight into the learner rank's buffer by the rollout kernels (NVLink peer stores); call `gather.finish()` after.
         """
         self._sample_count += 1
         cc = self._cc = compile_chain(self.env)
@@ -269,7 +272,8 @@ class ParallelRolloutSampler(SamplerBase):
                         params=None if distr is not None else (sim._params if sim._params is not None and
                                                                sim._params.shape[0] == num_envs else None),
                         distr=distr, seed=self._kernel_seed(), env_offset=rank * num_envs, episode=0,
-                        stop_on_done=True, auto_reset=auto_reset, record=record, traj=traj, row_flag=row_flag)
+                        stop_on_done=True, auto_reset=auto_reset, record=record or gather is not None,
+                        **(gather.target() if gather is not None else dict(traj=traj, row_flag=row_flag)))
         self.last_stats = sharding.allreduce_stats(res["stats"]) if self._shard is None else res["stats"]
         return res
 

@@ -81,3 +81,77 @@ def broadcast_policy(policy: torch.nn.Module, src: int = 0, group=None):
         return
     for p in policy.parameters():
         dist.broadcast(p.data, src=src, group=group)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Rollouts for the learner: the record shards of all ranks in one buffer on one rank
+# ---------------------------------------------------------------------------------------------------------------------
+def gather_records(traj: torch.Tensor, row_flag: torch.Tensor, n_total: int, dst: int = 0, group=None):
+    """Collective baseline (NCCL / gloo): every rank's time-major record shard [T, n_local, W] and flags [T, n_local] end
+    up on `dst` as [T, n_total, W] / [T, n_total] in global rollout order (blocks as cut by `shard_range`).  Returns
+    (traj, row_flag) on `dst`, (None, None) elsewhere.  The transfer FOLLOWS the simulation; `RecordGather` below makes
+    the rollout kernels write into the learner's memory directly instead."""
+    rank, ws = world(group)
+    if ws == 1:
+        return traj, row_flag
+    T, _, W = traj.shape
+    n_max = -(-n_total // ws)
+    pad_t = torch.zeros(T, n_max, W, dtype=traj.dtype, device=traj.device)
+    pad_f = torch.zeros(T, n_max, dtype=row_flag.dtype, device=row_flag.device)
+    pad_t[:, : traj.shape[1]] = traj
+    pad_f[:, : row_flag.shape[1]] = row_flag
+    parts_t = [torch.empty_like(pad_t) for _ in range(ws)] if rank == dst else None
+    parts_f = [torch.empty_like(pad_f) for _ in range(ws)] if rank == dst else None
+    dist.gather(pad_t, parts_t, dst=dst, group=group)
+    dist.gather(pad_f, parts_f, dst=dst, group=group)
+    if rank != dst:
+        return None, None
+    out_t = torch.empty(T, n_total, W, dtype=traj.dtype, device=traj.device)
+    out_f = torch.empty(T, n_total, dtype=row_flag.dtype, device=row_flag.device)
+    for r in range(ws):
+        lo, hi = shard_range(n_total, r, ws)
+        out_t[:, lo:hi] = parts_t[r][:, : hi - lo]
+        out_f[:, lo:hi] = parts_f[r][:, : hi - lo]
+    return out_t, out_f
+
+
+class RecordGather:
+    """The learner's record buffer as the DIRECT target of every rank's rollout launch ("gather rollouts for the
+    learner"): `traj` [T, n_total, W] and `row_flag` [T, n_total] live on rank `dst`, every other rank maps them through
+    torch's symmetric memory (CUDA peer mappings over NVLink / NVSwitch) and passes the mapped pointers to `sre_rollout`
+    with its column offset (`sre_rollout_io.traj_env_offset`).  The kernel's record tiles -- 128-bit streaming stores or
+    bulk (TMA) stores of a warp's 32 records -- then travel over NVLink while the simulation runs: one kernel does the
+    compute and the transfer, no collective follows.  `finish()` is the only synchronisation (a device-side barrier on
+    the launching stream after the kernel).
+
+    Every rank allocates the symmetric buffer (the allocation is collective and symmetric), so the size has to fit one
+    GPU: T * n_total * (W * 4 + 1) bytes."""
+
+    def __init__(self, n_rows: int, n_total: int, width: int, dtype=torch.float32, device=None, dst: int = 0, group=None):
+        self.rank, self.ws = world(group)
+        self.dst, self.n_total, self.group = dst, n_total, group
+        self.lo, self.hi = shard_range(n_total, self.rank, self.ws)
+        self._hdl_t = self._hdl_f = None
+        if self.ws == 1:
+            self.traj = torch.empty(n_rows, n_total, width, dtype=dtype, device=device)
+            self.row_flag = torch.empty(n_rows, n_total, dtype=torch.uint8, device=device)
+            return
+        import torch.distributed._symmetric_memory as symm
+
+        g = group if group is not None else dist.group.WORLD
+        self._local_t = symm.empty((n_rows, n_total, width), dtype=dtype, device=device)
+        self._local_f = symm.empty((n_rows, n_total), dtype=torch.uint8, device=device)
+        self._hdl_t = symm.rendezvous(self._local_t, group=g)
+        self._hdl_f = symm.rendezvous(self._local_f, group=g)
+        self.traj = self._hdl_t.get_buffer(dst, (n_rows, n_total, width), dtype)
+        self.row_flag = self._hdl_f.get_buffer(dst, (n_rows, n_total), torch.uint8)
+
+    def target(self) -> dict:
+        """Keyword arguments for engine.rollout / ParallelRolloutSampler.sample_batch of THIS rank."""
+        return dict(traj=self.traj, row_flag=self.row_flag, traj_env_offset=self.lo)
+
+    def finish(self):
+        """After the rollout launch(es): every rank's records have arrived on `dst` once this returns there."""
+        if self._hdl_t is not None:
+            self._hdl_t.barrier(channel=0)
+        return (self.traj, self.row_flag) if self.rank == self.dst else (None, None)

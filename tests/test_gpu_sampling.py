@@ -134,3 +134,25 @@ def test_full_size_fp32_properties(E):
     lo = 12345
     sub = E.rollout(cfg, pol, 4096, T, device=DEV, distr=distr, seed=0, env_offset=lo, auto_reset=True, record=False)
     assert torch.equal(sub["ret"], a["ret"][lo: lo + 4096]) and torch.equal(sub["length"], a["length"][lo: lo + 4096])
+
+
+def test_records_placed_inside_a_wider_buffer(E):
+    """sre_rollout_io.traj_env_stride / traj_env_offset: a launch writes its lanes into columns [offset, offset + n) of a
+    wider [T, M, W] buffer (the learner's buffer of a multi-GPU gather, sharding.RecordGather): same records as a launch
+    into its own buffer, the other columns untouched; both store paths (bulk tiles for the fused FNN, the 128-bit loop)."""
+    from simurlacra_b200 import _lib as L
+
+    H, n, M, off = 30, 96, 256, 64
+    for kind, sizes, do in ((L.QBB, [8, 16, 16, 2], 8), (L.QQ, [6, 10, 1], 6)):
+        cfg = E.make_cfg(kind, 0.01, H, dtype=torch.float32, act_norm=True)
+        w = _t((np.random.RandomState(2).randn(sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(len(sizes) - 1))) * 0.3), torch.float32)
+        pol = E.make_policy(L.POL_FNN, w, sizes=sizes)
+        own = E.rollout(cfg, pol, n, H + 1, device=DEV, seed=4, auto_reset=True)
+        width = own["traj"].shape[2]
+        wide_t = torch.full((H + 1, M, width), -7.0, dtype=torch.float32, device=DEV)
+        wide_f = torch.full((H + 1, M), 77, dtype=torch.uint8, device=DEV)
+        res = E.rollout(cfg, pol, n, H + 1, device=DEV, seed=4, auto_reset=True, traj=wide_t, row_flag=wide_f, traj_env_offset=off)
+        assert torch.equal(wide_t[:, off:off + n], own["traj"]) and torch.equal(wide_f[:, off:off + n], own["row_flag"])
+        assert torch.equal(res["obs"], own["obs"]) and torch.equal(res["ret"], own["ret"])
+        assert bool((wide_t[:, :off] == -7.0).all()) and bool((wide_t[:, off + n:] == -7.0).all())
+        assert bool((wide_f[:, :off] == 77).all()) and bool((wide_f[:, off + n:] == 77).all())

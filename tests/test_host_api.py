@@ -259,6 +259,15 @@ sharding.allreduce_stats(stats)
 assert stats.tolist() == [7.0, 28.0, 140.0, 70.0, 70.0, 0.0, 1.0, 7.0], stats
 full = sharding.allgather_ragged(ret, n_total)
 assert full.tolist() == [1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0], full
+T, W = 3, 2                                                     # record shards -> the learner (rank 0)
+traj = (torch.arange(lo, hi, dtype=torch.float32).view(1, -1, 1) + 100.0 * torch.arange(T).view(T, 1, 1)).expand(T, hi - lo, W).contiguous()
+flag = torch.arange(lo, hi, dtype=torch.uint8).view(1, -1).expand(T, hi - lo).contiguous()
+gt, gf = sharding.gather_records(traj, flag, n_total, dst=0)
+if rank == 0:
+    assert gt.shape == (T, n_total, W) and gt[2, :, 1].tolist() == [200.0 + i for i in range(n_total)], gt
+    assert gf[1].tolist() == list(range(n_total)), gf
+else:
+    assert gt is None and gf is None
 lin = torch.nn.Linear(3, 2)
 with torch.no_grad():
     lin.weight.fill_(float(rank + 1))
