@@ -96,6 +96,22 @@ extern "C" {
 #define SRE_FEAT_COS 7
 #define SRE_FEAT_SINSIN 8
 #define SRE_FEAT_SINCOS 9
+/* parametrised features (policies/features.py:157-161, :181-445); their parameters sit in sre_policy.feat_params at
+ * feat_arg[k] (floats):
+ *   SIG   sigmoid(scale x)            [scale]                         n_obs features
+ *   BELL  exp(-scale x^2)             [scale]                         n_obs features
+ *   MULT  prod_i x[idx_i]             [n, idx_0 .. idx_{n-1}]         1 feature          (MultFeat)
+ *   ATAN2 atan2(x[i_sin], x[i_cos])   [i_sin, i_cos]                  1 feature          (ATan2Feat)
+ *   RF    scale cos(freq x + shift)   [D, scale, freq[D][n_obs], shift[D]]   D features  (RFFeat)
+ *   RBF   exp(-scale_i (x_i - c_fi)^2), L1-normalised per input dimension (state_wise = 1) or over all of them (0),
+ *         feature index i F + f       [F, state_wise, scale[n_obs], centers[F][n_obs]]   F n_obs features (RBFFeat) */
+#define SRE_FEAT_SIG 10
+#define SRE_FEAT_BELL 11
+#define SRE_FEAT_MULT 12
+#define SRE_FEAT_ATAN2 13
+#define SRE_FEAT_RF 14
+#define SRE_FEAT_RBF 15
+#define SRE_MAX_FEAT_PARAMS 1024
 
 /* distribution kinds, domain_randomization/domain_parameter.py:135 (Uniform), :171 (Normal), :246 (Bernoulli) */
 #define SRE_DISTR_NORMAL 0    /* a = mean, b = std */
@@ -254,6 +270,11 @@ typedef struct sre_policy {
      * any other group_size reads the weights per lane from global memory. */
     int64_t group_size;
     int64_t n_groups;
+    /* parameters of the parametrised features of a Linear policy: HOST pointer to n_feat_params floats
+     * (<= SRE_MAX_FEAT_PARAMS, copied into the launch), feat_arg[k] = offset of feature k's block (see SRE_FEAT_SIG ..) */
+    const float *feat_params;
+    int32_t n_feat_params;
+    int32_t feat_arg[SRE_MAX_FEATS];
 } sre_policy;
 
 /* Inputs / outputs of one rollout launch.  Replaces rollout() (sampling/rollout.py:63) run for N envs by

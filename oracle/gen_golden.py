@@ -247,6 +247,34 @@ def gen_policy_forward():
     out["lin_W"] = W.numpy()
     out["lin_x"] = x.numpy()
     out["lin_y"] = y.numpy()
+    # parametrised features of the reference (features.py:157-161, :181-445): feature values and W @ feats for 1-dim inputs
+    import functools
+    from pyrado.policies.features import ATan2Feat, MultFeat, RBFFeat, RFFeat, bell_feat, sig_feat
+
+    torch.manual_seed(11)
+    d = 4
+    xp = torch.randn(16, d)
+    rf = RFFeat(inp_dim=d, num_feat_per_dim=12, bandwidth=np.array([1.0, 2.0, 0.5, 1.5]))
+    rbf_s = RBFFeat(num_feat_per_dim=5, bounds=(np.array([-2.0, -1.0, -3.0, -2.0]), np.array([2.0, 1.0, 3.0, 2.0])))
+    rbf_j = RBFFeat(num_feat_per_dim=4, bounds=(np.array([-2.0, -1.0, -3.0, -2.0]), np.array([2.0, 1.0, 3.0, 2.0])), scale=0.7,
+                    state_wise_norm=False)
+    stacks = dict(
+        elem=[const_feat, functools.partial(sig_feat, scale=1.7), functools.partial(bell_feat, scale=0.6), sig_feat,
+              MultFeat((0, 2)), MultFeat((1, 2, 3)), ATan2Feat(0, 1), identity_feat],
+        rf=[rf], rbf_state=[rbf_s], rbf_joint=[rbf_j])
+    for tag, fl in stacks.items():
+        vals = []
+        for i in range(xp.shape[0]):
+            vals.append(torch.cat([f(xp[i]).reshape(-1) for f in fl]))  # 1-dim input like a policy call (RF / RBF give [1, n])
+        F = torch.stack(vals)
+        Wp = torch.randn(2, F.shape[1]) * 0.3
+        out[f"pf_{tag}_feats"] = F.numpy()
+        out[f"pf_{tag}_W"] = Wp.numpy()
+        out[f"pf_{tag}_y"] = (F @ Wp.T).numpy()
+    out["pf_x"] = xp.numpy()
+    out["pf_rf_freq"], out["pf_rf_shift"], out["pf_rf_scale"] = rf.freq.numpy(), rf.shift.numpy(), np.float32(rf.scale)
+    out["pf_rbf_state_centers"], out["pf_rbf_state_scale"] = rbf_s.centers.numpy(), rbf_s.scale.numpy()
+    out["pf_rbf_joint_centers"], out["pf_rbf_joint_scale"] = rbf_j.centers.numpy(), np.float32(rbf_j.scale)
     np.savez_compressed(osp.join(OUT, "policy_forward.npz"), **out)
 
 
@@ -615,7 +643,8 @@ if __name__ == "__main__":
     if len(sys.argv) > 1:  # only the later additions (leaves the earlier files untouched)
         {"stab": gen_stab_envs, "returns": gen_returns, "pend": lambda: gen_env_trajs("pend", n_cases=6),
          "wrappers": gen_wrappers, "bob-d": lambda: gen_env_trajs("bob-d", n_cases=6), "calm": gen_calm_trajs,
-         "fnn64": gen_fnn_closed_loop_envs, "dr": gen_dr_moments, "diff": gen_diff_extras}[sys.argv[1]]()
+         "fnn64": gen_fnn_closed_loop_envs, "dr": gen_dr_moments, "diff": gen_diff_extras,
+         "policies": gen_policy_forward}[sys.argv[1]]()
         sys.exit(0)
     print("trajectories")
     gen_env_trajs("qq-su", n_cases=6)

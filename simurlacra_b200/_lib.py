@@ -26,7 +26,9 @@ PREC_FP32, PREC_TF32X3, PREC_TF32 = 0, 1, 2
 STEP_YIELDED_FINAL, STEP_COUNT_MASK = 1 << 30, 0x3FFFFFFF
 ACT_NOISE_NONE, ACT_NOISE_NORMAL, ACT_NOISE_UNIFORM = 0, 1, 2
 ENV_ACT_NOISE_NONE, ENV_ACT_NOISE_OUTER, ENV_ACT_NOISE_INNER = 0, 1, 2
-FEATS = dict(const=0, identity=1, sign=2, abs=3, squared=4, cubic=5, sin=6, cos=7, sinsin=8, sincos=9)
+FEATS = dict(const=0, identity=1, sign=2, abs=3, squared=4, cubic=5, sin=6, cos=7, sinsin=8, sincos=9, sig=10, bell=11,
+             mult=12, atan2=13, rf=14, rbf=15)
+MAX_FEAT_PARAMS = 1024
 DISTR_NORMAL, DISTR_UNIFORM, DISTR_BERNOULLI = 0, 1, 2
 ROW_STEP, ROW_DONE, ROW_TERMINAL, ROW_TRUNCATED, ROW_IDLE = 0, 1, 2, 3, 4
 ST_NAN_STATE, ST_NAN_ACT, ST_NAN_OBS = 1, 2, 4
@@ -135,6 +137,9 @@ class Policy(C.Structure):
         ("act_noise_mean", C.c_float * MAX_DA),
         ("group_size", C.c_int64),
         ("n_groups", C.c_int64),
+        ("feat_params", C.c_void_p),
+        ("n_feat_params", C.c_int32),
+        ("feat_arg", C.c_int32 * MAX_FEATS),
     ]
 
 

@@ -110,12 +110,45 @@ int make_kpolicy(const sre_policy *pol, int n_obs, int n_act, KPolicy &kp) {
         SRE_CHECK_ARG(pol->n_feats >= 1 && pol->n_feats <= SRE_MAX_FEATS, SRE_E_POLICY, "n_feats %d outside [1, %d]",
                       pol->n_feats, SRE_MAX_FEATS);
         int nf = 0;
+        SRE_CHECK_ARG(pol->n_feat_params >= 0 && pol->n_feat_params <= SRE_MAX_FEAT_PARAMS &&
+                          (pol->n_feat_params == 0 || pol->feat_params != nullptr),
+                      SRE_E_POLICY, "n_feat_params %d outside [0, %d] or feat_params NULL", pol->n_feat_params,
+                      SRE_MAX_FEAT_PARAMS);
+        for (int i = 0; i < pol->n_feat_params; i++) kp.fparams[i] = pol->feat_params[i];
         for (int i = 0; i < pol->n_feats; i++) {
-            SRE_CHECK_ARG(pol->feats[i] >= 0 && pol->feats[i] <= SRE_FEAT_SINCOS, SRE_E_POLICY, "unknown feature %d",
-                          pol->feats[i]);
-            kp.feats[i] = pol->feats[i];
-            nf += pol->feats[i] == SRE_FEAT_CONST ? 1 : n_obs;
+            const int fk = pol->feats[i];
+            SRE_CHECK_ARG(fk >= 0 && fk <= SRE_FEAT_RBF, SRE_E_POLICY, "unknown feature %d", fk);
+            kp.feats[i] = fk;
+            int dim = fk == SRE_FEAT_CONST ? 1 : n_obs;
+            if (fk >= SRE_FEAT_SIG) {  // parametrised: the block has to lie inside feat_params and index the observation
+                const int a = pol->feat_arg[i], left = pol->n_feat_params - a;
+                SRE_CHECK_ARG(a >= 0 && left >= 1, SRE_E_POLICY, "feature %d: parameter block at %d outside the %d floats", i,
+                              a, pol->n_feat_params);
+                const float *p = pol->feat_params + a;
+                if (fk == SRE_FEAT_MULT) {
+                    const int n = (int)p[0];
+                    SRE_CHECK_ARG(n >= 2 && n <= 8 && left >= 1 + n, SRE_E_POLICY, "MultFeat with %d indices", n);
+                    for (int j = 0; j < n; j++)
+                        SRE_CHECK_ARG((int)p[1 + j] >= 0 && (int)p[1 + j] < n_obs, SRE_E_POLICY, "MultFeat index %d", (int)p[1 + j]);
+                    dim = 1;
+                } else if (fk == SRE_FEAT_ATAN2) {
+                    SRE_CHECK_ARG(left >= 2 && (int)p[0] >= 0 && (int)p[0] < n_obs && (int)p[1] >= 0 && (int)p[1] < n_obs,
+                                  SRE_E_POLICY, "ATan2Feat indices out of range");
+                    dim = 1;
+                } else if (fk == SRE_FEAT_RF) {
+                    const int D = (int)p[0];
+                    SRE_CHECK_ARG(D >= 1 && left >= 2 + D * n_obs + D, SRE_E_POLICY, "RFFeat with %d features does not fit", D);
+                    dim = D;
+                } else if (fk == SRE_FEAT_RBF) {
+                    const int F = (int)p[0];
+                    SRE_CHECK_ARG(F >= 2 && left >= 2 + n_obs + F * n_obs, SRE_E_POLICY, "RBFFeat with %d centers does not fit", F);
+                    dim = F * n_obs;
+                }
+                kp.feat_arg[i] = a;
+            }
+            nf += dim;
         }
+        kp.n_lin_feats = nf;
         need = (long long)nf * n_act;
     } else {
         set_error("unknown policy kind %d", pol->kind);

@@ -22,6 +22,9 @@ struct KPolicy {
     int cta_groups;        // group_size is a multiple of the CTA size: one parameter set per CTA, staged like a single set
     int act_noise;    // SRE_ACT_NOISE_*
     float noise_scale[SRE_MAX_DA], noise_mean[SRE_MAX_DA];
+    int n_lin_feats;                       // Linear policy: total number of feature values (columns of W)
+    int feat_arg[SRE_MAX_FEATS];           // offset of feature k's parameter block in fparams
+    float fparams[SRE_MAX_FEAT_PARAMS];    // parameters of the parametrised features (host-validated copy)
 };
 
 SRE_DEV float nonlin_f(int kind, float x) {
@@ -258,49 +261,81 @@ SRE_DEV float feat_f(int kind, float x) {
     }
 }
 
-template <int N_OBS, int N_ACT>
-SRE_DEV void linear_forward(const KPolicy &pol, const float *sm, const float *obs, float *act) {
-    int nf = 0;
-    for (int k = 0; k < pol.n_feats; k++) nf += (pol.feats[k] == SRE_FEAT_CONST) ? 1 : N_OBS;
-#pragma unroll
-    for (int o = 0; o < N_ACT; o++) act[o] = 0.f;
+// act = W feats(obs), W [n_act][n_lin_feats] row-major, the feature values formed on the fly in stack order
+// (LinearPolicy.forward linear.py:95-110 over FeatureStack.__call__ features.py:66-75)
+SRE_DEV void linear_accumulate(const KPolicy &pol, const float *w, const float *obs, int n_obs, float *act, int n_act) {
+    const int nf = pol.n_lin_feats;
+    for (int o = 0; o < n_act; o++) act[o] = 0.f;
     int col = 0;
+    auto add = [&](float f) {
+        for (int o = 0; o < n_act; o++) act[o] = fmaf(w[o * nf + col], f, act[o]);
+        col++;
+    };
     for (int k = 0; k < pol.n_feats; k++) {
         const int fk = pol.feats[k];
+        const float *p = pol.fparams + pol.feat_arg[k];
         if (fk == SRE_FEAT_CONST) {
-#pragma unroll
-            for (int o = 0; o < N_ACT; o++) act[o] = fmaf(sm[o * nf + col], 1.0f, act[o]);
-            col += 1;
-        } else {
-#pragma unroll
-            for (int i = 0; i < N_OBS; i++) {
-                const float f = feat_f(fk, obs[i]);
-#pragma unroll
-                for (int o = 0; o < N_ACT; o++) act[o] = fmaf(sm[o * nf + col + i], f, act[o]);
+            add(1.0f);
+        } else if (fk <= SRE_FEAT_SINCOS) {
+            for (int i = 0; i < n_obs; i++) add(feat_f(fk, obs[i]));
+        } else if (fk == SRE_FEAT_SIG) {
+            for (int i = 0; i < n_obs; i++) add(1.0f / (1.0f + expf(-(p[0] * obs[i]))));
+        } else if (fk == SRE_FEAT_BELL) {
+            for (int i = 0; i < n_obs; i++) add(expf(-p[0] * (obs[i] * obs[i])));
+        } else if (fk == SRE_FEAT_MULT) {
+            const int n = (int)p[0];
+            float v = obs[(int)p[1]];
+            for (int j = 1; j < n; j++) v *= obs[(int)p[1 + j]];
+            add(v);
+        } else if (fk == SRE_FEAT_ATAN2) {
+            add(atan2f(obs[(int)p[0]], obs[(int)p[1]]));
+        } else if (fk == SRE_FEAT_RF) {
+            const int D = (int)p[0];
+            const float *freq = p + 2, *shift = p + 2 + D * n_obs;
+            for (int d = 0; d < D; d++) {
+                float s = 0.f;
+                for (int i = 0; i < n_obs; i++) s = fmaf(obs[i], freq[d * n_obs + i], s);
+                add(p[1] * cosf(s + shift[d]));
             }
-            col += N_OBS;
+        } else {  // SRE_FEAT_RBF
+            const int F = (int)p[0];
+            const bool state_wise = p[1] != 0.f;
+            const float *scale = p + 2, *cen = p + 2 + n_obs;
+            float tot = 0.f;
+            if (!state_wise) {
+                for (int i = 0; i < n_obs; i++)
+                    for (int f = 0; f < F; f++) {
+                        const float d = obs[i] - cen[f * n_obs + i];
+                        tot += expf(-scale[i] * (d * d));
+                    }
+                if (!(tot > 1e-8f)) tot = 1.0f;
+            }
+            for (int i = 0; i < n_obs; i++) {
+                float nrm = tot;
+                if (state_wise) {
+                    nrm = 0.f;
+                    for (int f = 0; f < F; f++) {
+                        const float d = obs[i] - cen[f * n_obs + i];
+                        nrm += expf(-scale[i] * (d * d));
+                    }
+                    if (!(nrm > 1e-8f)) nrm = 1.0f;
+                }
+                for (int f = 0; f < F; f++) {
+                    const float d = obs[i] - cen[f * n_obs + i];
+                    add(expf(-scale[i] * (d * d)) / nrm);
+                }
+            }
         }
     }
 }
 
+template <int N_OBS, int N_ACT>
+SRE_DEV void linear_forward(const KPolicy &pol, const float *sm, const float *obs, float *act) {
+    linear_accumulate(pol, sm, obs, N_OBS, act, N_ACT);
+}
+
 SRE_DEV void linear_forward_rt(const KPolicy &pol, const float *w, const float *obs, int n_obs, float *act, int n_act) {
-    int nf = 0;
-    for (int k = 0; k < pol.n_feats; k++) nf += (pol.feats[k] == SRE_FEAT_CONST) ? 1 : n_obs;
-    for (int o = 0; o < n_act; o++) act[o] = 0.f;
-    int col = 0;
-    for (int k = 0; k < pol.n_feats; k++) {
-        const int fk = pol.feats[k];
-        if (fk == SRE_FEAT_CONST) {
-            for (int o = 0; o < n_act; o++) act[o] = fmaf(w[o * nf + col], 1.0f, act[o]);
-            col += 1;
-        } else {
-            for (int i = 0; i < n_obs; i++) {
-                const float f = feat_f(fk, obs[i]);
-                for (int o = 0; o < n_act; o++) act[o] = fmaf(w[o * nf + col + i], f, act[o]);
-            }
-            col += n_obs;
-        }
-    }
+    linear_accumulate(pol, w, obs, n_obs, act, n_act);
 }
 
 }  // namespace sre

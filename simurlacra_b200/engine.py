@@ -183,8 +183,19 @@ def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), fea
     for i, s in enumerate(sizes):
         p.sizes[i] = int(s)
     p.n_feats = len(feats)
+    blocks = []  # a feature is a name / code, or (name, [parameters]) for the parametrised ones (include/sre.h SRE_FEAT_SIG ..)
     for i, f in enumerate(feats):
+        if isinstance(f, (tuple, list)):
+            p.feat_arg[i] = sum(len(b) for b in blocks)
+            blocks.append([float(v) for v in f[1]])
+            f = f[0]
         p.feats[i] = L.FEATS[f] if isinstance(f, str) else int(f)
+    if blocks:
+        flat = [v for b in blocks for v in b]
+        if len(flat) > L.MAX_FEAT_PARAMS:
+            raise ValueError(f"{len(flat)} feature parameters, the kernel holds {L.MAX_FEAT_PARAMS}")
+        p._feat_keep = (C.c_float * len(flat))(*flat)  # HOST array, copied into the launch by the library
+        p.feat_params, p.n_feat_params = C.cast(p._feat_keep, C.c_void_p), len(flat)
     p.hidden_nonlin, p.output_nonlin, p.cartpole_feats = hidden_nonlin, output_nonlin, int(cartpole_feats)
     p.precision = int(precision)
     if weights is not None:

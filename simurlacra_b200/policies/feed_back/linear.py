@@ -49,8 +49,10 @@ class LinearPolicy(Policy):
         return act if batched else act.flatten()
 
     def engine_desc(self, device, param_sets=None, group_size: int = 0):
-        codes = self._feats.engine_codes()
+        codes = self._feats.engine_codes(self.env_spec.obs_space.flat_dim)
         if codes is None or len(codes) > L.MAX_FEATS:
             return None
+        if sum(len(c[1]) for c in codes if isinstance(c, tuple)) > L.MAX_FEAT_PARAMS:
+            return None  # e.g. hundreds of random Fourier features: evaluated as a torch module
         weights = self._engine_weights(device) if param_sets is None else param_sets
         return E.make_policy(L.POL_LINEAR, weights, feats=codes, group_size=group_size)

@@ -146,6 +146,47 @@ def test_policy_forward_golden(E):
     np.testing.assert_allclose(y, g["lin_y"], rtol=2e-5, atol=2e-5)
 
 
+def test_parametrised_linear_features_golden(E):
+    """sig / bell / MultFeat / ATan2Feat / RFFeat / RBFFeat inside the Linear-policy kernel (csrc/sre_policy.cuh
+    linear_accumulate) against W @ feats of the unmodified reference (policies/features.py:157-161, :181-445), through the
+    LinearPolicy class and as a fused policy inside a rollout launch."""
+    import functools
+
+    from simurlacra_b200 import _lib as L
+    from simurlacra_b200.policies.features import (ATan2Feat, FeatureStack, MultFeat, RBFFeat, RFFeat, bell_feat, const_feat,
+                                                   identity_feat, sig_feat)
+
+    g = golden("policy_forward")
+    rf = RFFeat(inp_dim=4, num_feat_per_dim=12, bandwidth=1.0)
+    rf.freq, rf.shift, rf.scale = torch.from_numpy(g["pf_rf_freq"]), torch.from_numpy(g["pf_rf_shift"]), torch.tensor(float(g["pf_rf_scale"]))
+    bounds = (np.array([-2.0, -1.0, -3.0, -2.0]), np.array([2.0, 1.0, 3.0, 2.0]))
+    stacks = dict(elem=[const_feat, functools.partial(sig_feat, scale=1.7), functools.partial(bell_feat, scale=0.6), sig_feat,
+                        MultFeat((0, 2)), MultFeat((1, 2, 3)), ATan2Feat(0, 1), identity_feat],
+                  rf=[rf], rbf_state=[RBFFeat(num_feat_per_dim=5, bounds=bounds)],
+                  rbf_joint=[RBFFeat(num_feat_per_dim=4, bounds=bounds, scale=0.7, state_wise_norm=False)])
+    x = _t(g["pf_x"], torch.float32)
+    for tag, fl in stacks.items():
+        codes = FeatureStack(*fl).engine_codes(4)
+        pol = E.make_policy(L.POL_LINEAR, _t(g[f"pf_{tag}_W"].reshape(-1), torch.float32), feats=codes)
+        y = E.policy_forward(pol, x, 2).cpu().numpy()
+        np.testing.assert_allclose(y, g[f"pf_{tag}_y"], rtol=3e-5, atol=3e-5, err_msg=tag)
+    # inside a rollout launch: OneMassOscillator (2 observations, 1 action) with an RBF + ATan2 stack, fused against stepping
+    from simurlacra_b200.environments.pysim.one_mass_oscillator import OneMassOscillatorSim
+    from simurlacra_b200.policies.feed_back.linear import LinearPolicy
+    from simurlacra_b200.sampling import rollout
+    from simurlacra_b200.sampling.rollout import compile_chain
+
+    env = OneMassOscillatorSim(dt=0.02, max_steps=40)
+    torch.manual_seed(2)
+    pol = LinearPolicy(env.spec, FeatureStack(const_feat, RBFFeat(3, bounds=(np.array([-1.0, -2.0]), np.array([1.0, 2.0]))),
+                                              ATan2Feat(0, 1), functools.partial(bell_feat, scale=0.5)))
+    assert pol.engine_desc(env.device) is not None and compile_chain(env) is not None
+    fused = rollout(env, pol, seed=1, reset_kwargs=dict(init_state=np.array([0.3, -0.2])))
+    loop = rollout(env, pol, seed=1, record_dts=True, reset_kwargs=dict(init_state=np.array([0.3, -0.2])))
+    np.testing.assert_allclose(fused.actions, loop.actions, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(fused.observations, loop.observations, rtol=1e-4, atol=1e-5)
+
+
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_fnn_closed_loop_golden(E, dtype):
     """Config C1: QQube + FNN in closed loop against the reference run (torch CPU policy, numpy env); covers the

@@ -156,3 +156,24 @@ def test_records_placed_inside_a_wider_buffer(E):
         assert torch.equal(res["obs"], own["obs"]) and torch.equal(res["ret"], own["ret"])
         assert bool((wide_t[:, :off] == -7.0).all()) and bool((wide_t[:, off + n:] == -7.0).all())
         assert bool((wide_f[:, :off] == 77).all()) and bool((wide_f[:, off + n:] == 77).all())
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpu_record_gather_over_peer_memory():
+    """sharding.RecordGather on 2 GPUs (torchrun, NCCL + symmetric memory): the learner's buffer filled by both ranks'
+    rollout kernels is bit-identical to the NCCL gather of the local record buffers (tools/gather_bench.py exits 1 else)."""
+    import os
+    import os.path as osp
+    import socket
+    import subprocess
+    import sys
+
+    root = osp.dirname(osp.dirname(osp.abspath(__file__)))
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", str(port), osp.join(root, "tools", "gather_bench.py"), "--envs", "4096",
+                        "--workload", "qbb", "--reps", "1"], capture_output=True, text=True, timeout=280, env=dict(os.environ))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert '"parity_peer_equals_nccl_gather": true' in r.stdout

@@ -555,3 +555,44 @@ def test_discounted_values_return_shapes_match_reference():
         if tag == "eq":
             assert a.shape == g["dvs_eq_numpy"].shape
             np.testing.assert_allclose(a, g["dvs_eq_numpy"], rtol=1e-12)
+
+
+def test_parametrised_features_match_reference_values():
+    """MultFeat / ATan2Feat / RFFeat / RBFFeat / sig / bell (policies/features.py:157-161, :181-445) against feature values
+    of the unmodified reference (tests/golden/policy_forward.npz, `oracle/gen_golden.py policies`), single and batched
+    inputs, the kernel codes they hand to the Linear-policy kernel, and the feature count."""
+    import functools
+
+    from conftest import golden
+    from simurlacra_b200.policies.features import (ATan2Feat, FeatureStack, MultFeat, RBFFeat, RFFeat, bell_feat, const_feat,
+                                                   identity_feat, sig_feat)
+
+    g = golden("policy_forward")
+    x = torch.from_numpy(g["pf_x"])
+    rf = RFFeat(inp_dim=4, num_feat_per_dim=12, bandwidth=1.0)
+    rf.freq, rf.shift, rf.scale = torch.from_numpy(g["pf_rf_freq"]), torch.from_numpy(g["pf_rf_shift"]), torch.tensor(float(g["pf_rf_scale"]))
+    bounds = (np.array([-2.0, -1.0, -3.0, -2.0]), np.array([2.0, 1.0, 3.0, 2.0]))
+    rbf_s = RBFFeat(num_feat_per_dim=5, bounds=bounds)
+    rbf_j = RBFFeat(num_feat_per_dim=4, bounds=bounds, scale=0.7, state_wise_norm=False)
+    np.testing.assert_allclose(rbf_s.centers.numpy(), g["pf_rbf_state_centers"], rtol=1e-6)
+    np.testing.assert_allclose(rbf_s.scale.numpy(), g["pf_rbf_state_scale"], rtol=1e-6)
+    stacks = dict(elem=[const_feat, functools.partial(sig_feat, scale=1.7), functools.partial(bell_feat, scale=0.6), sig_feat,
+                        MultFeat((0, 2)), MultFeat((1, 2, 3)), ATan2Feat(0, 1), identity_feat],
+                  rf=[rf], rbf_state=[rbf_s], rbf_joint=[rbf_j])
+    for tag, fl in stacks.items():
+        fs = FeatureStack(*fl)
+        ref = g[f"pf_{tag}_feats"]
+        assert fs.get_num_feat(4) == ref.shape[1]
+        if tag == "elem":  # batched call of a mixed stack (the reference's MultFeat / ATan2Feat take 1-dim inputs only)
+            np.testing.assert_allclose(fs(x).numpy(), ref, rtol=1e-5, atol=1e-6)
+        one = torch.stack([torch.cat([f(x[i]).reshape(-1) for f in fl]) for i in range(x.shape[0])])
+        np.testing.assert_allclose(one.numpy(), ref, rtol=1e-5, atol=1e-6)
+        codes = fs.engine_codes(4)
+        assert codes is not None and len(codes) == len(fl)
+    assert FeatureStack(lambda t: t).engine_codes(4) is None and FeatureStack(RFFeat(3, 4, 1.0)).engine_codes(4) is None
+    with pytest.raises(pyrado.TypeErr):
+        MultFeat([0, 1])
+    with pytest.raises(pyrado.ShapeErr):
+        MultFeat((0,))
+    with pytest.raises(pyrado.ValueErr):
+        RBFFeat(1, bounds)

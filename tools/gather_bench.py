@@ -57,6 +57,8 @@ def main():
     peer_step(7)
     torch.cuda.synchronize()
     dist.barrier()
+    mine_ok = bool(torch.equal(gat.traj[:, gat.lo:gat.hi].view(torch.int32), run.extra["traj"].view(torch.int32)))
+    print(f"rank {rank}: its columns of the learner buffer equal its local records: {mine_ok}", file=sys.stderr, flush=True)
     ok = True
     if rank == 0:  # peer_step already ran the barrier on every rank: rank 0's own buffer is complete
         # bit patterns: a lane that diverged holds NaN records on both routes
@@ -64,8 +66,13 @@ def main():
         bad_f = (gat.row_flag != ref_f).any(dim=0)
         ok = not bool(bad_t.any()) and not bool(bad_f.any())
         if not ok:
+            d = (gat.traj.view(torch.int32) != ref_t.view(torch.int32))
+            idx = d.nonzero()[0].tolist()
+            print("first mismatch (row, lane, col)", idx, float(gat.traj[tuple(idx)]), float(ref_t[tuple(idx)]), "frac", float(d.float().mean()),
+                  "ref peer half all zero:", bool((ref_t[:, n:] == 0).all()), file=sys.stderr, flush=True)
             print("mismatching lanes: traj own", int(bad_t[:n].sum()), "peer", int(bad_t[n:].sum()), "flag own",
                   int(bad_f[:n].sum()), "peer", int(bad_f[n:].sum()), file=sys.stderr, flush=True)
+    dist.barrier()  # the other ranks must not start the next launches (which write into rank 0's buffer) before the comparison is done
     del ref_t, ref_f
 
     def timed(fn, k):
