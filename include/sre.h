@@ -432,7 +432,9 @@ int sre_qcp_diff_grad_static(const sre_env_cfg *cfg, const void *params, const v
 /* ---- measurement helpers (roofline denominators measured on the box) ---------------------- */
 /* FMA-only kernel: every thread runs `iters` x 32 dependent-free FFMA (dtype F32) or DFMA (F64); dtype 2: the same on
  * packed fma.rn.f32x2; dtype 3 / 4: FFMA / FFMA2 whose three operands are distinct, changing registers (the form
- * simulation code issues: no immediate, constant-bank or reuse-cache operand).
+ * simulation code issues: no immediate, constant-bank or reuse-cache operand); dtype 5 / 6 / 7: per iteration 16 such FFMA2,
+ * 8 MUFU.EX2, or both (do the FMA and the XU pipe overlap?); dtype 8 .. 11: 16 packed instructions per iteration by operand
+ * form (fma2 with a loop-invariant register / a launch-uniform operand, mul2 of two registers, add2 with an immediate).
  * Returns FLOPs issued in *flops; time it with CUDA events on `stream`. */
 int sre_bench_fma(int dtype, int64_t iters, int blocks, int threads, float *sink, double *flops, void *stream);
 /* streaming write of `bytes` with 128-bit stores (the HBM-write denominator) */

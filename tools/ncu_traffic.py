@@ -28,7 +28,9 @@ def dram_bytes(rep):
 
 def main():
     key, rep, units, what = sys.argv[1], sys.argv[2], float(sys.argv[3]), sys.argv[4]
-    path = osp.join(ROOT, "profiles", "r02_traffic.json")
+    import os
+
+    path = os.environ.get("SRE_TRAFFIC_JSON") or osp.join(ROOT, "profiles", "r02_traffic.json")
     d = json.load(open(path)) if osp.exists(path) else {}
     b = dram_bytes(rep)
     d[key] = dict(dram_bytes=b, units=units, bytes_per_unit=b / units, source=f"ncu --set full, {osp.basename(rep)}: {what}")
