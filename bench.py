@@ -525,7 +525,8 @@ def main():
 
         def e2e_step(i):
             res = sampler.sample_batch(N, auto_reset=True, record=wl["record"], **run.extra)
-            return res["ret"].cpu(), res["length"].cpu(), sampler.last_stats.cpu()
+            ret, ln, st = sampler.read_results(res)  # pinned staging buffers of the sampler, one synchronisation
+            return float(ret[0]), int(ln[0]), torch.from_numpy(st.copy())
 
         for i in range(2):
             e2e_step(i)
@@ -534,8 +535,8 @@ def main():
         head = dict(value=value, t_dev=t_dev, clk=clk, launches=run.launches, episodes_per_launch=episodes,
                     e2e=dict(value=e2e_value, unit="env-steps/s", h2d_bytes_per_step=int(policy.num_param * 4),
                              d2h_bytes_per_step=int(N * 8 + 64),
-                             call="ParallelRolloutSampler.sample_batch(N): policy parameters from pinned host memory, "
-                                  "returns + lengths + statistics read back to the host"),
+                             call="ParallelRolloutSampler.sample_batch(N) + read_results(): policy parameters from pinned host memory, "
+                                  "returns + lengths + statistics read back into pinned host buffers"),
                     roofline=roofline_for(wl, value / world, peaks, fma_peak, N, steps_per_launch=value / world * t_dev / K),
                     config=dict(workload=wl["label"], envs_per_gpu=N, horizon=wl["H"], auto_reset=True,
                                 trajectory="full records in HBM" if wl["record"] else "returns+lengths+stats",
@@ -630,11 +631,17 @@ def run_diff(E, L, torch, dev, n, h, K, warmup, timed, wall_timed, peaks, fma_pe
     t_f, _ = timed(lambda i: fwd(i) and None, K)
     rate_fb, rate_f = K * n * h * world / t_fb, K * n * h * world / t_f
 
-    def e2e_step(i):  # host buffers in, gradients out
+    out_h = (torch.empty(n, 4).pin_memory(), torch.empty(h, n).pin_memory(), torch.empty(n).pin_memory())
+
+    def e2e_step(i):  # pinned host buffers in, gradients and returns out into pinned host buffers
         s0d, actd = s0_h.to(dev, non_blocking=True), act_h.to(dev, non_blocking=True)
         states, thdd, rew, done = E.qcp_diff_forward(dcfg, None, s0d, actd)
         g_s0, g_act, _ = E.qcp_diff_backward(dcfg, None, states, thdd, actd, g_rew=g_rew)
-        return g_s0.cpu(), g_act.cpu(), rew.sum(0).cpu()
+        out_h[0].copy_(g_s0, non_blocking=True)
+        out_h[1].copy_(g_act, non_blocking=True)
+        out_h[2].copy_(rew.sum(0), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(out_h[2][0])
 
     for i in range(2):
         e2e_step(i)

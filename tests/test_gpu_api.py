@@ -326,8 +326,13 @@ def test_sample_batch_device_resident():
     assert 0.98 * 5000 * 120 <= st["num_steps"] <= 5000 * 120 and st["num_rollouts"] >= 5000
     assert st["num_steps"] + st["num_rollouts"] >= 5000 * 120
     assert st["min_return"] <= st["avg_return"] <= st["max_return"]
+    ret_h, len_h, st_h = s.read_results(res)  # pinned staging buffers of the sampler
+    np.testing.assert_array_equal(ret_h, res["ret"].cpu().numpy())
+    np.testing.assert_array_equal(len_h, res["length"].cpu().numpy())
+    np.testing.assert_array_equal(st_h, s.last_stats.cpu().numpy())
     rec = s.sample_batch(512, auto_reset=False, record=True)
     assert rec["traj"].shape[:2] == (121, 512) and int(rec["length"].max()) <= 120
+    assert s.read_results(rec)[0].shape == (512,)
 
 
 def test_step_diff_state_autograd_matches_reference():
