@@ -173,7 +173,10 @@ class ParallelRolloutSampler(SamplerBase):
             # ---- a minimum number of steps: rollout indices 0, 1, 2, ... in order until both limits hold; the
             # result is cut after the first index that satisfies them, so it does not depend on the chunking
             horizon = int(sim.max_steps)
-            chunk = min(self.max_lanes, max(self.min_rollouts or 1, ceil(self.min_steps / horizon)))
+            # lanes per launch: episodes rarely use the whole horizon, and a launch of a few dozen lanes costs the same ~2 ms as
+            # one of a few hundred (it is latency-bound), so the first launch over-provisions four-fold -- the result is cut
+            # after the first index that satisfies the limits either way
+            chunk = min(self.max_lanes, max(self.min_rollouts or 1, 4 * ceil(self.min_steps / horizon)))
             lengths, results, done_n = [], [], 0
             n_keep = None
             while n_keep is None:
