@@ -96,6 +96,81 @@ template <typename R> SRE_DEV R m_sign(R x) { return (R)((x > (R)0) - (x < (R)0)
 template <typename R> SRE_DEV bool m_isnan(R x) { return x != x; }
 
 // ------------------------------------------------------------------------------------------------------
+// packed FP32 pairs (Blackwell add / mul / fma .f32x2: two values per issue slot).  Cost on a scheduler's FMA pipe
+// (profiles/r02_pipe_microbench.json): 2.0 cycles per warp instruction with an immediate / uniform / two-register form, 2.3
+// with one reused register, 3.1 with three changing registers.
+// ------------------------------------------------------------------------------------------------------
+SRE_DEV unsigned long long pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+SRE_DEV void unpack2(unsigned long long v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+SRE_DEV unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
+// packed FP32 pairs (Blackwell add/mul/fma .f32x2: two lanes per issue slot)
+SRE_DEV unsigned long long add2(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+SRE_DEV unsigned long long mul2(unsigned long long a, unsigned long long b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+struct P2 {
+    unsigned long long v;
+};
+SRE_DEV P2 p2(float a, float b) { return P2{pack2(a, b)}; }
+SRE_DEV P2 p2s(float a) { return P2{pack2(a, a)}; }
+SRE_DEV P2 operator+(P2 a, P2 b) { return P2{add2(a.v, b.v)}; }
+SRE_DEV P2 operator*(P2 a, P2 b) { return P2{mul2(a.v, b.v)}; }
+SRE_DEV P2 pfma(P2 a, P2 b, P2 c) { return P2{fma2(a.v, b.v, c.v)}; }
+SRE_DEV P2 psub(P2 a, P2 b) { return P2{fma2(b.v, pack2(-1.0f, -1.0f), a.v)}; }  // a - b, exact product
+SRE_DEV void pun(P2 a, float &x, float &y) { unpack2(a.v, x, y); }
+
+// m_sincos for a pair.  q = rint(x 2/pi) comes from the magic-number addition (the integer sits in the low mantissa bits
+// of t, two's complement, so its parity / bit 1 are read from there): no FRND / F2I.
+SRE_DEV void sincos2(P2 x, P2 &s, P2 &c) {
+    const P2 magic = p2s(12582912.0f);
+    const P2 t = pfma(x, p2s(0.63661977236758138f), magic);
+    const P2 q = psub(t, magic);
+    P2 r = pfma(q, p2s(-0x1.921fb6p+0f), x);
+    r = pfma(q, p2s(0x1.777a5cp-25f), r);
+    r = pfma(q, p2s(0x1.ee59dap-50f), r);
+    const P2 z = r * r;
+    P2 ps = pfma(pfma(p2s(-1.9515295891e-4f), z, p2s(8.3321608736e-3f)), z, p2s(-1.6666654611e-1f));
+    ps = pfma(ps * z, r, r);
+    P2 pc = pfma(pfma(p2s(2.443315711809948e-5f), z, p2s(-1.388731625493765e-3f)), z, p2s(4.166664568298827e-2f));
+    pc = pfma(pc * z, z, pfma(p2s(-0.5f), z, p2s(1.0f)));
+    float ps0, ps1, pc0, pc1;
+    pun(ps, ps0, ps1);
+    pun(pc, pc0, pc1);
+    const int i0 = (int)(unsigned)t.v, i1 = (int)(unsigned)(t.v >> 32);
+    const bool o0 = i0 & 1, o1 = i1 & 1;
+    const float s0 = __int_as_float(__float_as_int(o0 ? pc0 : ps0) ^ ((i0 & 2) << 30));
+    const float c0 = __int_as_float(__float_as_int(o0 ? ps0 : pc0) ^ (((i0 + 1) & 2) << 30));
+    const float s1 = __int_as_float(__float_as_int(o1 ? pc1 : ps1) ^ ((i1 & 2) << 30));
+    const float c1 = __int_as_float(__float_as_int(o1 ? ps1 : pc1) ^ (((i1 + 1) & 2) << 30));
+    s = p2(s0, s1);
+    c = p2(c0, c1);
+}
+SRE_DEV P2 rcp2_neg(P2 nx) {  // 1 / (-nx) for a pair (m_rcp): two MUFU seeds (operand negation is free there), one packed Newton step
+    float x0, x1, r0, r1;
+    pun(nx, x0, x1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(-x0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(-x1));
+    const P2 r = p2(r0, r1);
+    return pfma(r, pfma(nx, r, p2s(1.0f)), r);
+}
+
+
+// ------------------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al., SC'11; Random123 constants)
 // Engine addressing: key = (seed_lo, seed_hi); counter = (env_lo, env_hi, episode, stream << 24 | block)
 // ------------------------------------------------------------------------------------------------------

@@ -74,8 +74,16 @@ template <typename R> struct Env<SRE_QQ, R> {
         s[3] += dt * aldd;
     }
     SRE_DEV static void observe(const R *s, R *obs, R *trig) {  // :148-149
-        m_sincos(s[0], obs[0], obs[1]);
-        m_sincos(s[1], obs[2], obs[3]);
+        if constexpr (sizeof(R) == 4) {  // float build: the two angles as one packed pair (15 packed + 16 scalar instructions for both)
+            P2 sn, cs;
+            sincos2(p2((float)s[0], (float)s[1]), sn, cs);
+            float a, b;
+            pun(sn, a, b); obs[0] = (R)a; obs[2] = (R)b;
+            pun(cs, a, b); obs[1] = (R)a; obs[3] = (R)b;
+        } else {
+            m_sincos(s[0], obs[0], obs[1]);
+            m_sincos(s[1], obs[2], obs[3]);
+        }
         obs[4] = s[2];
         obs[5] = s[3];
         trig[0] = obs[2];
@@ -265,6 +273,52 @@ template <typename R> struct Env<SRE_QBB, R> {
         const bool simple = flags & SRE_F_SIMPLE_DYN;
         if (!simple && c.Vxn <= act[0] && act[0] <= c.Vxp) act[0] = (R)0;  // dead zones :261-264 (in place)
         if (!simple && c.Vyn <= act[1] && act[1] <= c.Vyp) act[1] = (R)0;
+        if constexpr (sizeof(R) == 4) {
+            // Production (float) build: the two axes of the plate are the same formulas on (x, y) pairs -- servo angles,
+            // plate angles, ball positions and all their derivatives -- so the whole step runs on packed f32x2 arithmetic
+            // with the pair {x axis, y axis} in one register pair: two sincos2 instead of four sincos, one packed Newton
+            // step for the two reciprocals, every update one instruction for both axes.  Same operation order as the scalar
+            // code below (which the fp64 verification build runs); the y axis' sign flips sit in the constants.
+            const P2 pdt = p2s((float)dt);
+            const P2 th = p2((float)s[0], (float)s[1]) + p2((float)c.off_x, (float)c.off_y);
+            const P2 thd = p2((float)s[4], (float)s[5]);
+            const P2 thdd = pfma(p2s(-(float)c.k_vel), thd, p2s((float)c.k_act) * p2((float)act[0], (float)act[1]));
+            P2 sxy, cxy, sab, cab;
+            sincos2(th, sxy, cxy);
+            sincos2(p2((float)h[0], (float)h[1]), sab, cab);
+            // 1 / cos of the plate angles (m_rcp): MUFU seeds + one packed Newton step
+            float ca, cb, ra, rb;
+            pun(cab, ca, cb);
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(ca));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cb));
+            const P2 r0 = p2(ra, rb);
+            const P2 icab = psub(r0, r0 * pfma(cab, r0, p2s(-1.0f)));
+            const P2 ck = p2((float)c.c_kin, -(float)c.c_kin);  // a_dot = c_kin thxd cx / ca, b_dot = -c_kin thyd cy / cb
+            const P2 abd = ((ck * thd) * cxy) * icab;
+            const P2 abd2 = abd * abd;
+            P2 acc;
+            if (simple) {
+                acc = p2s((float)c.kx_g) * sxy;
+            } else {
+                const P2 t = psub(thdd * cxy, (thd * thd) * sxy);
+                const P2 abdd = icab * pfma(ck, t, abd2 * sab);
+                acc = pfma(p2s(-(float)c.kx_J), abdd, p2s(-(float)c.kx_damp) * p2((float)s[6], (float)s[7]));
+                acc = pfma(p2s((float)c.kx_m) * p2((float)s[2], (float)s[3]), abd2, acc);
+                acc = pfma(p2s((float)c.kx_g), sxy, acc);
+            }
+            const P2 hn = pfma(abd, pdt, p2((float)h[0], (float)h[1]));
+            const P2 s45 = pfma(thdd, pdt, thd);
+            const P2 s67 = pfma(acc, pdt, p2((float)s[6], (float)s[7]));
+            const P2 s01 = pfma(s45, pdt, p2((float)s[0], (float)s[1]));
+            const P2 s23 = pfma(s67, pdt, p2((float)s[2], (float)s[3]));
+            float o0, o1;
+            pun(hn, o0, o1); h[0] = (R)o0; h[1] = (R)o1;
+            pun(s01, o0, o1); s[0] = (R)o0; s[1] = (R)o1;
+            pun(s23, o0, o1); s[2] = (R)o0; s[3] = (R)o1;
+            pun(s45, o0, o1); s[4] = (R)o0; s[5] = (R)o1;
+            pun(s67, o0, o1); s[6] = (R)o0; s[7] = (R)o1;
+            return;
+        }
         const R th_x = s[0] + c.off_x, th_y = s[1] + c.off_y;
         const R thxd = s[4], thyd = s[5];
         const R thxdd = c.k_act * act[0] - c.k_vel * thxd;  // :276-277

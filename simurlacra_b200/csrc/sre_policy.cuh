@@ -45,18 +45,6 @@ SRE_DEV float nonlin_f(int kind, float x) {
 // Layer 1 (IN <= 8 inputs) and the dynamics stay thread-per-env; layer 3 is folded into the epilogue of layer 2
 // and reduced across the 8 lanes of a row group with a transpose-reduce (7 shuffles), which leaves the action of
 // environment e on lane e.
-SRE_DEV unsigned long long pack2(float lo, float hi) {
-    unsigned long long r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-SRE_DEV void unpack2(unsigned long long v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-SRE_DEV unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
-    unsigned long long d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-}
-
 // tanh(z) = 1 - 2 / (1 + e^(2z)).  The caller passes zs = 2 log2(e) z (the scale is folded into the weights and
 // biases of the producing layer when they are staged), so this is MUFU.EX2, FADD, MUFU.RCP, FFMA: four
 // instructions, absolute error < 3e-7; saturates correctly (ex2 -> inf gives rcp -> 0, ex2 -> 0 gives -1).

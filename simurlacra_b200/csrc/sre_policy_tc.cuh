@@ -19,12 +19,6 @@ namespace sre {
 
 SRE_DEV uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// packed FP32 pairs (Blackwell add/mul/fma .f32x2: two lanes per issue slot)
-SRE_DEV unsigned long long add2(unsigned long long a, unsigned long long b) {
-    unsigned long long d;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
 // tanh of a packed pair of prescaled arguments (see tanh_prescaled), ONE reciprocal for both lanes:
 //   a_i = 1 + 2^(z_i);  r = 1 / (a_0 a_1);  1/a_0 = r a_1, 1/a_1 = r a_0;  tanh_i = 1 - 2 / a_i
 // 3 MUFU per pair instead of 4 (the XU pipe, 16 lanes/clk/SM, is the scarcest unit of this kernel).  The arguments are
@@ -55,11 +49,6 @@ SRE_DEV unsigned long long tanh2_prescaled(unsigned long long zs) {
 #endif
 }
 
-SRE_DEV unsigned long long mul2(unsigned long long a, unsigned long long b) {
-    unsigned long long d;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
 // Two packed pairs at once: the shared reciprocal pairs lane i of `za` with lane i of `zb`, so that the products and
 // the two back-multiplications stay packed (a_i b_i, then 1/a_i = r_i b_i and 1/b_i = r_i a_i): per 4 tanh
 // 4 FMNMX + 4 EX2 + 2 FADD2 + 3 FMUL2 + 2 RCP + 2 FFMA2 = 17 issue slots instead of 20.
