@@ -107,10 +107,18 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
 #ifndef SRE_FNN_BLOCKS
 #define SRE_FNN_BLOCKS 2  // resident 256-thread CTAs per SM of the fused-FNN (CUDA-core) variants of the float build
 #endif
+#ifndef SRE_FNN16_THREADS
+#define SRE_FNN16_THREADS 256
+#endif
+#ifndef SRE_FNN16_BLOCKS
+#define SRE_FNN16_BLOCKS 2
+#endif
 template <typename R, int PV> struct LaunchShape {
     static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile
-    static constexpr int THREADS = TC ? 128 : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128);
-    static constexpr int MIN_BLOCKS = TC ? SRE_TC_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? SRE_FNN_BLOCKS : 1);
+    static constexpr bool LANE16 = PV == SRE_PV_FNN16 && sizeof(R) == 4;  // register-resident FNN16: no warp cooperation
+    static constexpr int THREADS = TC ? 128 : (LANE16 ? SRE_FNN16_THREADS : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128));
+    static constexpr int MIN_BLOCKS =
+        TC ? SRE_TC_BLOCKS : (LANE16 ? SRE_FNN16_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? SRE_FNN_BLOCKS : 1));
 };
 
 template <int KIND, typename R> SRE_DEV float qbb_plate_ang(R arm_radius, R plate_length, R th_in) {
