@@ -136,6 +136,42 @@ def test_full_size_fp32_properties(E):
     assert torch.equal(sub["ret"], a["ret"][lo: lo + 4096]) and torch.equal(sub["length"], a["length"][lo: lo + 4096])
 
 
+def test_c4_records_at_scale_properties(E):
+    """BASELINE config 4 (QBallBalancer + 20-parameter DR + fused FNN[16,16], full StepSequence records; 2^18 lanes x 500
+    steps = 12 GB of records through the bulk-store path) through size-independent properties: the row flags account for every
+    row, step rows sum to the statistics, the first episode's rewards sum to the lane's return, the observation of the
+    ball balancer IS the state on every written row, closing rows carry no action / reward, and a shard re-run alone
+    reproduces its records bit for bit."""
+    from simurlacra_b200 import _lib as L
+    from simurlacra_b200.domain_randomization.default_randomizers import create_default_randomizer_qbb
+    from simurlacra_b200.environments.pysim.quanser_ball_balancer import QBallBalancerSim
+
+    N, H = 1 << 18, 500
+    cfg = E.make_cfg(L.QBB, 0.01, H, dtype=torch.float32, act_norm=True)
+    sizes = [8, 16, 16, 2]
+    w = _t(np.random.RandomState(1).randn(sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(3))) * 0.3, torch.float32)
+    pol = E.make_policy(L.POL_FNN, w, sizes=sizes)
+    distr = create_default_randomizer_qbb().table(QBallBalancerSim._param_names)
+    res = E.rollout(cfg, pol, N, H + 1, device=DEV, distr=distr, seed=2, auto_reset=True)
+    flag, st = res["row_flag"], res["stats"].cpu().numpy()
+    assert int(res["status"].abs().sum()) == 0
+    stepped = (flag == L.ROW_STEP) | (flag == L.ROW_DONE)
+    closing = (flag == L.ROW_TERMINAL) | (flag == L.ROW_TRUNCATED)
+    assert int(stepped.sum()) == st[L.STAT_STEPS] and bool((stepped | closing).all())  # auto-reset: no idle rows
+    assert int((flag == L.ROW_TERMINAL).sum()) == st[L.STAT_EPISODES]
+    # first episode of every lane: rewards up to its length sum to the lane's return
+    t = torch.arange(H + 1, device=DEV).view(-1, 1)
+    first = t < res["length"].view(1, -1)
+    ret = (res["rew"] * first).sum(dim=0)
+    assert float((ret - res["ret"]).abs().max()) < 1e-3 * max(1.0, float(res["ret"].abs().max()))
+    assert bool(stepped[first].all())
+    assert torch.equal(res["obs"], res["state"])  # QBB observes its state (quanser_ball_balancer.py observe), closing rows included
+    assert float(res["act"][closing].abs().max()) == 0.0 and float(res["rew"][closing].abs().max()) == 0.0
+    lo, n = 98304, 2048
+    sub = E.rollout(cfg, pol, n, H + 1, device=DEV, distr=distr, seed=2, env_offset=lo, auto_reset=True)
+    assert torch.equal(sub["traj"], res["traj"][:, lo:lo + n]) and torch.equal(sub["row_flag"], flag[:, lo:lo + n])
+
+
 def test_records_placed_inside_a_wider_buffer(E):
     """sre_rollout_io.traj_env_stride / traj_env_offset: a launch writes its lanes into columns [offset, offset + n) of a
     wider [T, M, W] buffer (the learner's buffer of a multi-GPU gather, sharding.RecordGather): same records as a launch
