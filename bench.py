@@ -338,7 +338,8 @@ class RolloutRunner:
         w = fnn_weights(wl["sizes"], seed=wl["wseed"] if wseed is None else wseed)
         self.w = torch.from_numpy(w).to(dev)
         kw = dict(act_noise=L.ACT_NOISE_NORMAL, act_noise_scale=[0.1] * wl["sizes"][-1]) if act_noise else {}
-        self.pol = E.make_policy(L.POL_FNN, self.w, sizes=wl["sizes"], precision=wl["prec"] if prec is None else prec, **kw)
+        self.pol = E.make_policy(L.POL_FNN, self.w, sizes=wl["sizes"], precision=wl["prec"] if prec is None else prec,
+                                 weights_host=torch.from_numpy(w), **kw)  # the host copy: small layers as launch arguments
         self.extra = {}
         if wl["record"]:
             lay = E.record_layout(wl["kind"])

@@ -275,6 +275,9 @@ typedef struct sre_policy {
     const float *feat_params;
     int32_t n_feat_params;
     int32_t feat_arg[SRE_MAX_FEATS];
+    /* optional HOST copy of `weights` (same layout, n_weights floats, read during the call): lets sre_rollout pass the small
+     * layers of a [in,64,64,out] tensor-core policy as launch arguments instead of staging them in shared memory */
+    const float *weights_host;
 } sre_policy;
 
 /* Inputs / outputs of one rollout launch.  Replaces rollout() (sampling/rollout.py:63) run for N envs by

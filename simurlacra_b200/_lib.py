@@ -140,6 +140,7 @@ class Policy(C.Structure):
         ("feat_params", C.c_void_p),
         ("n_feat_params", C.c_int32),
         ("feat_arg", C.c_int32 * MAX_FEATS),
+        ("weights_host", C.c_void_p),
     ]
 
 

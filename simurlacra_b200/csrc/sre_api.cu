@@ -447,6 +447,34 @@ int sre_rollout(const sre_env_cfg *cfg, const sre_policy *pol, const sre_rollout
                   "the fused linear policy needs the full observation (got %d of %d entries)", n_pol_in, k_do[kind]);
     e = make_kpolicy(pol, n_pol_in, k_da[kind], kp);
     if (e) return e;
+    // small layers of the tensor-core policy as launch arguments (FnnTC2's layout: W1^T, b1, b2 prescaled, W3, b3)
+    if (pol->weights_host && pol->kind == SRE_POL_FNN && pol->n_layers == 3 && pol->sizes[1] == 64 && pol->sizes[2] == 64 &&
+        pol->group_size == 0 && pol->sizes[0] <= 8 && pol->sizes[3] <= 2 && pol->hidden_nonlin == 0 && pol->output_nonlin == 0) {
+        const int IN = pol->sizes[0], OUT = pol->sizes[3], H = 64;
+        const float PRE = SRE_TANH_PRESCALE;
+        const float *W1 = pol->weights_host, *b1 = W1 + IN * H, *W2 = b1 + H, *b2 = W2 + H * H, *W3 = b2 + H, *b3 = W3 + OUT * H;
+        float *c = kp.cw;
+        for (int i = 0; i < IN * H; i++) c[(i % IN) * H + i / IN] = PRE * W1[i];
+        for (int i = 0; i < H; i++) { c[IN * H + i] = PRE * b1[i]; c[IN * H + H + i] = PRE * b2[i]; }
+        for (int i = 0; i < OUT * H; i++) c[IN * H + 2 * H + i] = W3[i];
+        for (int i = 0; i < 4; i++) c[IN * H + 2 * H + OUT * H + i] = i < OUT ? b3[i] : 0.f;
+        kp.has_cw = 1;
+    }
+    if (pol->weights_host && pol->kind == SRE_POL_FNN && pol->n_layers == 3 && pol->sizes[1] == 16 && pol->sizes[2] == 16 &&
+        pol->group_size == 0 && pol->sizes[0] <= 8 && pol->sizes[3] <= 2 && pol->hidden_nonlin == 0 && pol->output_nonlin == 0) {
+        // FnnLane16's layout (sre_policy_tc.cuh): W1^T [IN][16], b1, W2^T [16][16], b2 (prescaled), W3^T [16][2 OP], b3
+        const int IN = pol->sizes[0], OUT = pol->sizes[3], H = 16, OP = (OUT + 1) / 2;
+        const int oB1 = IN * H, oW2 = oB1 + H, oB2 = oW2 + H * H, oW3 = oB2 + H, oB3 = oW3 + H * 2 * OP;
+        const float PRE = SRE_TANH_PRESCALE;
+        const float *W1 = pol->weights_host, *b1 = W1 + IN * H, *W2 = b1 + H, *b2 = W2 + H * H, *W3 = b2 + H, *b3 = W3 + OUT * H;
+        float *c = kp.cw;
+        for (int i = 0; i < IN * H; i++) c[(i % IN) * H + i / IN] = PRE * W1[i];
+        for (int i = 0; i < H * H; i++) c[oW2 + (i % H) * H + i / H] = PRE * W2[i];
+        for (int i = 0; i < H; i++) { c[oB1 + i] = PRE * b1[i]; c[oB2 + i] = PRE * b2[i]; }
+        for (int i = 0; i < H * 2 * OP; i++) c[oW3 + i] = (i % (2 * OP)) < OUT ? W3[(i % (2 * OP)) * H + i / (2 * OP)] : 0.f;
+        for (int i = 0; i < 2 * OP; i++) c[oB3 + i] = i < OUT ? b3[i] : 0.f;
+        kp.has_cw = 2;
+    }
     SRE_CHECK_ARG(!kp.cartpole_feats, SRE_E_UNSUPPORTED,
                   "cartpole_feats (the fork's 4-dim FNNPolicy input) is only available in sre_policy_forward");
     if (kp.group_size > 0)

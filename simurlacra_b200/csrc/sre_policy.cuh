@@ -9,6 +9,7 @@
 
 namespace sre {
 
+#define SRE_TC_CW_FLOATS (8 * 64 + 64 + 64 + 2 * 64 + 8)
 struct KPolicy {
     int kind, n_layers;
     int sizes[SRE_MAX_LAYERS + 1];
@@ -25,6 +26,10 @@ struct KPolicy {
     int n_lin_feats;                       // Linear policy: total number of feature values (columns of W)
     int feat_arg[SRE_MAX_FEATS];           // offset of feature k's parameter block in fparams
     float fparams[SRE_MAX_FEAT_PARAMS];    // parameters of the parametrised features (host-validated copy)
+    // tensor-core policy: W1^T / b1 / b2 (prescaled), W3, b3 as LAUNCH ARGUMENTS (constant bank -> uniform-register operands)
+    // when the caller has the parameters on the host (sre_policy.weights_host); layout of FnnTC2's shared-memory block
+    int has_cw;
+    alignas(16) float cw[SRE_TC_CW_FLOATS];
 };
 
 SRE_DEV float nonlin_f(int kind, float x) {
@@ -57,6 +62,7 @@ SRE_DEV float tanh_prescaled(float zs) {
 }
 
 template <int IN, int HID, int OUT, bool FAST_TANH> struct FnnTiled {
+    static constexpr bool TAKES_CW = false;
     static constexpr int TN = HID / 8;  // outputs per lane
     static constexpr int NM = TN / 2;   // 16-output chunks
     static_assert(HID % 16 == 0 && HID <= 64, "hidden width must be 16, 32 or 64");

@@ -16,7 +16,7 @@ __global__ void __launch_bounds__(128) policy_forward_tc_kernel(const __grid_con
     float x[IN], a[OUT];
 #pragma unroll
     for (int i = 0; i < IN; i++) x[i] = n < N ? obs[n * IN + i] : 0.f;
-    F::forward(c, x, a);
+    F::forward(c, x, a, pol.cw);
     if (n < N) {
 #pragma unroll
         for (int i = 0; i < OUT; i++) act[n * OUT + i] = a[i];

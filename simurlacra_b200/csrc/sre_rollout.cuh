@@ -9,6 +9,7 @@
 #include "sre_policy.cuh"
 #include "sre_policy_tc.cuh"
 #include <cstdlib>
+#include <type_traits>
 
 namespace sre {
 
@@ -19,11 +20,13 @@ namespace sre {
 #define SRE_PV_FNN16 16
 #define SRE_PV_FNN32 32
 #define SRE_PV_FNN64 64
+#define SRE_PV_FNN16W 116  // SRE_PV_FNN16 (float build) with the weights as launch arguments (sre_policy.weights_host given)
 #ifndef SRE_COOP_MAX_LANES
 #define SRE_COOP_MAX_LANES 5  // up to this many restarting lanes of a warp draw their parameters cooperatively
 #endif
 #define SRE_PV_TC 1000    // [do,64,64,da] tanh, hidden layer on the tensor cores, 3 x TF32 (sre_policy_tc.cuh)
 #define SRE_PV_TC1 1001   // the same, single TF32 pass
+#define SRE_PV_TCW 1002   // SRE_PV_TC with layer 1 / biases / layer 3 as launch arguments (sre_policy.weights_host given)
 
 struct KIO {
     long long n_envs, n_rows;
@@ -115,7 +118,7 @@ SRE_DEV void atomic_max_double(double *addr, double v) {
 #endif
 template <typename R, int PV> struct LaunchShape {
     static constexpr bool TC = PV >= SRE_PV_TC;  // one CTA = one 128-row UMMA tile
-    static constexpr bool LANE16 = PV == SRE_PV_FNN16 && sizeof(R) == 4;  // register-resident FNN16: no warp cooperation
+    static constexpr bool LANE16 = (PV == SRE_PV_FNN16 || PV == SRE_PV_FNN16W) && sizeof(R) == 4;  // register-resident FNN16: no warp cooperation
     static constexpr int THREADS = TC ? 128 : (LANE16 ? SRE_FNN16_THREADS : ((PV >= 16 && sizeof(R) == 4) ? 256 : 128));
     static constexpr int MIN_BLOCKS =
         TC ? SRE_TC_BLOCKS : (LANE16 ? SRE_FNN16_BLOCKS : ((PV >= 16 && sizeof(R) == 4) ? SRE_FNN_BLOCKS : 1));
@@ -231,9 +234,10 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
     constexpr bool WRAP = MODE == SRE_MODE_GENERIC && PV < 16;  // the bodies that can run the stateful step wrappers
     constexpr int NIN = WRAP ? SRE_MAX_POL_IN : DO;
     // verification build (double) keeps the accurate tanhf; the production build uses the 2-MUFU form
-    using Fast = FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>;
+    using Fast = std::conditional_t<PV == SRE_PV_FNN16W, FnnLane16<DO, DA, true>,
+                                    FnnTiled<DO, ((PV >= 16 && PV <= 64) ? PV : 16), DA, sizeof(R) == 4>>;
     constexpr bool TC = PV >= SRE_PV_TC;
-    using Tc = FnnTC2<DO, DA, PV == SRE_PV_TC1>;
+    using Tc = FnnTC2<DO, DA, PV == SRE_PV_TC1, PV == SRE_PV_TCW>;
     typename Tc::Ctx tc;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -508,8 +512,11 @@ rollout_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ KDis
                 if (!record && !want_flag && !io.auto_reset && (row & 15) == 0) {
                     if (!__syncthreads_or(lane_state != IDLE)) break;
                 }
-                Tc::forward(tc, of, af);
-            } else if (PV >= 16) Fast::forward(sm_w, h1s, of, af, lane);
+                Tc::forward(tc, of, af, pol.cw);
+            } else if (PV >= 16) {
+                if constexpr (Fast::TAKES_CW) Fast::forward(sm_w, h1s, of, af, lane, pol.cw);
+                else Fast::forward(sm_w, h1s, of, af, lane);
+            }
             else {
                 // parameter exploration: this lane's own parameter set, straight from global memory (L2-resident)
                 const float *wsrc = per_lane_w ? pol.weights + (valid ? n / pol.group_size : 0) * pol.n_weights : sm_w;
@@ -773,8 +780,11 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
     }
     if (two_hidden && pol.sizes[1] == 64 && pol.precision != SRE_PREC_FP32 && sizeof(R) == 4) {
         pol.smem_floats = 0;
-        return pol.precision == SRE_PREC_TF32 ? launch_rollout_pv<KIND, R, SRE_PV_TC1>(cfg, distr, pol, io, stream)
-                                              : launch_rollout_pv<KIND, R, SRE_PV_TC>(cfg, distr, pol, io, stream);
+        if (pol.precision == SRE_PREC_TF32) return launch_rollout_pv<KIND, R, SRE_PV_TC1>(cfg, distr, pol, io, stream);
+        const char *nocw = getenv("SRE_NO_CW");  // A/B measurements and tests: ignore the host copy of the weights
+        if (pol.has_cw == 1 && !pol.cta_groups && !(nocw && nocw[0] == '1'))
+            return launch_rollout_pv<KIND, R, SRE_PV_TCW>(cfg, distr, pol, io, stream);
+        return launch_rollout_pv<KIND, R, SRE_PV_TC>(cfg, distr, pol, io, stream);
     }
     if (two_hidden && pol.sizes[1] == 64) {
         pol.smem_floats = FnnTiled<E::DO, 64, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
@@ -786,6 +796,9 @@ int launch_rollout(const KCfg<R> &cfg, const KDistr &distr, KPolicy pol, const K
     }
     if (two_hidden && pol.sizes[1] == 16) {
         pol.smem_floats = FnnTiled<E::DO, 16, E::DA, sizeof(R) == 4>::SMEM_FLOATS;
+        const char *nocw = getenv("SRE_NO_CW");
+        if (sizeof(R) == 4 && pol.has_cw == 2 && !pol.cta_groups && !(nocw && nocw[0] == '1'))
+            return launch_rollout_pv<KIND, R, SRE_PV_FNN16W>(cfg, distr, pol, io, stream);
         return launch_rollout_pv<KIND, R, SRE_PV_FNN16>(cfg, distr, pol, io, stream);
     }
     pol.smem_floats = (int)((pol.n_weights + 3) / 4 * 4);

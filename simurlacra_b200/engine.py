@@ -170,7 +170,7 @@ def make_distr_table(entries: Sequence[dict]):
 
 def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), feats=(), hidden_nonlin: int = 0,
                 output_nonlin: int = 0, cartpole_feats: bool = False, precision: int = L.PREC_TF32X3, act_noise: int = 0,
-                act_noise_scale=(), act_noise_mean=(), group_size: int = 0) -> L.Policy:
+                act_noise_scale=(), act_noise_mean=(), group_size: int = 0, weights_host=None) -> L.Policy:
     """`group_size` > 0: `weights` is a [n_sets, n_weights] matrix of parameter sets and lane n of a rollout launch
     evaluates set n // group_size (parameter-exploration sampling).
     `precision`: arithmetic of a [in, 64, 64, out] tanh network's hidden layer in the float32 build -- L.PREC_TF32X3
@@ -198,6 +198,12 @@ def make_policy(kind: int, weights: Optional[torch.Tensor] = None, sizes=(), fea
         p.feat_params, p.n_feat_params = C.cast(p._feat_keep, C.c_void_p), len(flat)
     p.hidden_nonlin, p.output_nonlin, p.cartpole_feats = hidden_nonlin, output_nonlin, int(cartpole_feats)
     p.precision = int(precision)
+    if weights_host is not None and not group_size:  # optional host copy (float32, contiguous, CPU) of the same parameters
+        wh = weights_host if isinstance(weights_host, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(weights_host, dtype=np.float32))
+        if wh.is_cuda or wh.dtype != torch.float32 or not wh.is_contiguous() or (weights is not None and wh.numel() != weights.numel()):
+            raise ValueError("weights_host must be a contiguous float32 CPU tensor with as many entries as weights")
+        p._keep_host = wh
+        p.weights_host = wh.data_ptr()
     if weights is not None:
         if not (weights.is_cuda and weights.dtype == torch.float32 and weights.is_contiguous()):
             raise ValueError("policy weights must be a contiguous float32 CUDA tensor")

@@ -118,6 +118,7 @@ class Policy(nn.Module, ABC):
         update that the reference does by pickling the state_dict to every worker)."""
         with torch.no_grad():
             v = self.param_values.detach()
+            self._host_weights = None
             if v.is_cuda:
                 return v.to(device=device, dtype=torch.float32).contiguous()
             device = torch.device(device)
@@ -129,6 +130,7 @@ class Policy(nn.Module, ABC):
                 # change under it (the earlier launch would silently run with these later weights)
                 self._pinned_free.synchronize()
             self._pinned.copy_(v)
+            self._host_weights = self._pinned  # the same parameters on the host: sre_policy.weights_host (read at launch time)
             dev = self._dev_weights.get(device)
             if dev is None or dev.numel() != v.numel():
                 dev = self._dev_weights[device] = torch.empty(v.numel(), dtype=torch.float32, device=device)

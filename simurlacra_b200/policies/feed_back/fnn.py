@@ -134,6 +134,7 @@ class FNNPolicy(Policy):
         if codes is None:
             return None
         weights = self._engine_weights(device) if param_sets is None else param_sets
+        host = getattr(self, "_host_weights", None) if param_sets is None else None  # small layers travel as launch arguments
         return E.make_policy(L.POL_FNN, weights, sizes=self.net.sizes, hidden_nonlin=codes[0],
                              output_nonlin=codes[1], cartpole_feats=self.cartpole_feats,
-                             precision=self.engine_precision, group_size=group_size)
+                             precision=self.engine_precision, group_size=group_size, weights_host=host)

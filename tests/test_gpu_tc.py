@@ -262,3 +262,32 @@ def test_specialised_bodies_and_prepared_starts_reproduce_the_generic_kernel(E, 
     assert float(same.float().mean()) > 0.99
     torch.testing.assert_close(a["ret"][same], b["ret"][same], rtol=2e-4, atol=2e-4)
     assert abs(float(a["stats"][L.STAT_STEPS]) - float(b["stats"][L.STAT_STEPS])) <= 0.01 * float(b["stats"][L.STAT_STEPS])
+
+
+@pytest.mark.parametrize("kind_name,sizes", [("QQ", [6, 64, 64, 1]), ("QCP", [5, 64, 64, 1]), ("QBB", [8, 64, 64, 2]),
+                                             ("QBB", [8, 16, 16, 2]), ("QQ", [6, 16, 16, 1])])
+def test_launch_argument_weights_are_bit_identical(E, kind_name, sizes):
+    """sre_policy.weights_host: the small layers of the tensor-core policy (and the whole FNN[16,16]) travel as launch
+    arguments and are read as uniform-register operands (rollout_kernel<.., SRE_PV_TCW / SRE_PV_FNN16W>) instead of shared
+    memory.  Same arithmetic in the same order: returns, lengths, records and statistics are bit-identical to the launch
+    without the host copy, in the plain, the recording and the generic (exploration noise) bodies."""
+    from simurlacra_b200 import _lib as L
+
+    kind = getattr(L, kind_name)
+    rng = np.random.RandomState(4)
+    w = (rng.randn(sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(3))) * 0.3).astype(np.float32)
+    wd = torch.from_numpy(w).to(DEV)
+    cfg = E.make_cfg(kind, 0.01, 80, dtype=torch.float32, act_norm=True, **(dict(long_pole=True) if kind_name == "QCP" else {}))
+    N = 1000
+    for record, noise in ((False, False), (True, False), (True, True)):
+        kw = dict(act_noise=L.ACT_NOISE_NORMAL, act_noise_scale=[0.1] * sizes[-1]) if noise else {}
+        out = []
+        for host in (None, torch.from_numpy(w)):
+            pol = E.make_policy(L.POL_FNN, wd, sizes=sizes, weights_host=host, **kw)
+            out.append(E.rollout(cfg, pol, N, 81, device=DEV, seed=6, auto_reset=True, record=record))
+        a, b = out
+        assert torch.equal(a["ret"], b["ret"]) and torch.equal(a["length"], b["length"])
+        # the statistics are accumulated with atomics across CTAs: the sums agree to the order of the additions
+        assert torch.allclose(a["stats"], b["stats"], rtol=1e-12, atol=0)
+        if record:
+            assert torch.equal(a["traj"].view(torch.int32), b["traj"].view(torch.int32)) and torch.equal(a["row_flag"], b["row_flag"])

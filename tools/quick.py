@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--tag", default="")
     ap.add_argument("--no-dr", action="store_true")
     ap.add_argument("--wseed", type=int, default=-1)
+    ap.add_argument("--host-weights", action="store_true", help="also pass the parameters as a host copy (sre_policy.weights_host)")
     a = ap.parse_args()
     import torch
 
@@ -64,7 +65,7 @@ def main():
     if a.no_dr:
         distr = None
     cfg = E.make_cfg(kind, dt, H, dtype=torch.float32, act_norm=True, **kw)
-    pol = E.make_policy(L.POL_FNN, w, sizes=sizes, precision=a.prec)
+    pol = E.make_policy(L.POL_FNN, w, sizes=sizes, precision=a.prec, weights_host=w.cpu() if a.host_weights else None)
     extra = {}
     if a.record:
         lay = E.record_layout(kind)
