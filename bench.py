@@ -543,6 +543,8 @@ def main():
                                 trajectory="full records in HBM" if wl["record"] else "returns+lengths+stats",
                                 policy_hidden_layer={0: "fp32 FMA (CUDA cores)", 1: "tcgen05 3xTF32 split (fp32-level accuracy)",
                                                      2: "tcgen05 TF32"}[wl["prec"]],
+                                policy_small_layers="launch arguments: the host copy of the parameters (sre_policy.weights_host) "
+                                                    "puts layer 1 / biases / layer 3 into the constant bank",
                                 l2="flushed between timed iterations (256 MB fill)", parallelism=f"env-shard x{world}"))
         if wl["tensor"]:
             extras["roofline_fp32"] = head["roofline"].pop("fp32_view")

@@ -25,16 +25,16 @@ quick_cap() {  # quick_cap <tag> <traffic key> <what> <quick.py args...>
     summarise "$tag" "$(steps_of gpurun_out/${tag}_plain.log)" "$key" "$what; without the profiler: $line"
     echo "$tag: $line"
 }
-quick_cap r02_f_headline qq_tc "rollout_kernel<QQ,float,TC,PLAIN>, 2^20 envs x 600 (C2, headline)" --workload qq --prec 1
-quick_cap r02_f_c4 qbb_rec "rollout_kernel<QBB,float,FNN16,PLAIN_REC>, 2^20 envs x 500, full records, bench policy (C4)" --workload qbb --record --envs 1048576 --wseed 1
-quick_cap r02_f_c3 qcp_tc "rollout_kernel<QCP,float,TC,PLAIN>, 2^20 envs x 600 (C3)" --workload qcp --prec 1
-python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > gpurun_out/prof/r02_f_c5_plain.log 2>&1 || { echo "diff bench failed"; exit 1; }
-$NCU -k regex:qcp_diff_forward2_kernel --launch-skip 3 -c 1 -o gpurun_out/r02_f_c5_forward python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > /dev/null 2>&1; echo "c5 fwd ncu $?"
-summarise r02_f_c5_forward 78643200 c5_forward "qcp_diff_forward2_kernel (two environments per thread), 2^18 envs x 300 (C5 forward)"
-$NCU -k regex:qcp_diff_backward_kernel --launch-skip 3 -c 1 -o gpurun_out/r02_f_c5_backward python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > /dev/null 2>&1; echo "c5 bwd ncu $?"
-summarise r02_f_c5_backward 78643200 c5_backward "qcp_diff_backward_kernel<float>, 2^18 envs x 300 (C5 adjoint)"
-$NCU -k regex:returns_kernel --launch-skip 2 -c 1 -o gpurun_out/r02_f_returns python bench.py --no-cpu-baseline --steps 2 > /dev/null 2>&1; echo "returns ncu $?"
-summarise r02_f_returns 630194176 returns_601x1M "returns_kernel<float,true,4>, [601, 2^20] rows (returns-to-go + GAE)"
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/prof/r02_f_launches_bench.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2>&1; echo "launch list $?"
-python tools/ncu_summary.py --launches gpurun_out/prof/r02_f_launches_bench.csv --out gpurun_out/prof/r02_f_launches_bench.txt > /dev/null 2>&1
+quick_cap r02_h_headline qq_tc "rollout_kernel<QQ,float,TCW,PLAIN>, 2^20 envs x 600 (C2, headline; policy weights as launch arguments)" --workload qq --prec 1 --host-weights
+quick_cap r02_h_c4 qbb_rec "rollout_kernel<QBB,float,FNN16W,PLAIN_REC>, 2^20 envs x 500, full records, bench policy (C4; policy weights as launch arguments)" --workload qbb --record --envs 1048576 --wseed 1 --host-weights
+quick_cap r02_h_c3 qcp_tc "rollout_kernel<QCP,float,TCW,PLAIN>, 2^20 envs x 600 (C3; policy weights as launch arguments)" --workload qcp --prec 1 --host-weights
+python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > gpurun_out/prof/r02_h_c5_plain.log 2>&1 || { echo "diff bench failed"; exit 1; }
+$NCU -k regex:qcp_diff_forward2_kernel --launch-skip 3 -c 1 -o gpurun_out/r02_h_c5_forward python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > /dev/null 2>&1; echo "c5 fwd ncu $?"
+summarise r02_h_c5_forward 78643200 c5_forward "qcp_diff_forward2_kernel (two environments per thread), 2^18 envs x 300 (C5 forward)"
+$NCU -k regex:qcp_diff_backward_kernel --launch-skip 3 -c 1 -o gpurun_out/r02_h_c5_backward python bench.py --workload diff --no-cpu-baseline --no-extras --steps 2 > /dev/null 2>&1; echo "c5 bwd ncu $?"
+summarise r02_h_c5_backward 78643200 c5_backward "qcp_diff_backward_kernel<float>, 2^18 envs x 300 (C5 adjoint)"
+$NCU -k regex:returns_kernel --launch-skip 2 -c 1 -o gpurun_out/r02_h_returns python bench.py --no-cpu-baseline --steps 2 > /dev/null 2>&1; echo "returns ncu $?"
+summarise r02_h_returns 630194176 returns_601x1M "returns_kernel<float,true,4>, [601, 2^20] rows (returns-to-go + GAE)"
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/prof/r02_h_launches_bench.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2>&1; echo "launch list $?"
+python tools/ncu_summary.py --launches gpurun_out/prof/r02_h_launches_bench.csv --out gpurun_out/prof/r02_h_launches_bench.txt > /dev/null 2>&1
 du -sh gpurun_out
