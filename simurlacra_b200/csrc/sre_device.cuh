@@ -8,6 +8,7 @@
 #include "../../include/sre.h"
 
 #define SRE_DEV __device__ __forceinline__
+#define SRE_HD __host__ __device__ __forceinline__  // also evaluated on the host (constants passed as launch arguments)
 #define SRE_PI 3.14159265358979323846
 
 namespace sre {

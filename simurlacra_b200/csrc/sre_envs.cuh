@@ -119,7 +119,7 @@ template <typename R> struct Env<SRE_QCP, R> {
         R thold_neg, thold_pos;
         R x_max, xd_max;       // the two state bounds that depend on rail_length
     };
-    SRE_DEV static void derive(const R *dp, int flags, Consts &c) {
+    SRE_HD static void derive(const R *dp, int flags, Consts &c) {
         const double g = dp[0], m_c = dp[1], l_rail = dp[2], eta_m = dp[3], eta_g = dp[4], K_g = dp[5], J_m = dp[6],
                      r_mp = dp[7], R_m = dp[8], k_m = dp[9], B_p = dp[10], B_eq = dp[11], m_p = dp[12], l_p = dp[13],
                      mu_c = dp[14];
@@ -140,7 +140,7 @@ template <typename R> struct Env<SRE_QCP, R> {
         c.x_max = (R)(l_rail / 2.0 - 0.15);  // _create_spaces :541-549, x_buffer = 0.15 (:79)
         c.xd_max = (R)l_rail;
     }
-    SRE_DEV static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    SRE_HD static void bounds(const Consts &c, int flags, R *st_lo, R *st_up, R *act_lo, R *act_up) {
         st_up[0] = c.x_max; st_up[1] = (R)(4 * SRE_PI); st_up[2] = c.xd_max; st_up[3] = (R)(20 * SRE_PI);
 #pragma unroll
         for (int i = 0; i < 4; i++) st_lo[i] = -st_up[i];

@@ -172,17 +172,48 @@ SRE_DEV void qcp_load_consts(const KCfg<R> &cfg, const R *params, long long n, t
     Env<SRE_QCP, R>::bounds(c, cfg.flags, st_lo, st_up, act_lo, act_up);
 }
 
+// Without per-environment parameters (params == NULL: the sac_wgrad use, nominal cart-pole) the derived constants are
+// the same for every lane: the host derives them once (Env::derive / bounds are host + device functions) and passes them
+// as a launch argument, so that they are constant-bank operands of the arithmetic (FFMA R, R, c[..], R at the full rate of
+// the FMA pipe instead of the three-register rate, and no registers) and the fp64 derive prologue disappears.
+template <typename R> struct QcpUni {
+    typename Env<SRE_QCP, R>::Consts c;
+    R st_lo[4], st_up[4], act_lo, act_up;
+};
+template <typename R> static void qcp_make_uni(const KCfg<R> &cfg, QcpUni<R> &u) {
+    R dp[Env<SRE_QCP, R>::DP];
+    for (int i = 0; i < Env<SRE_QCP, R>::DP; i++) dp[i] = cfg.base_params[i];
+    Env<SRE_QCP, R>::derive(dp, cfg.flags, u.c);
+    R al[1], au[1];
+    Env<SRE_QCP, R>::bounds(u.c, cfg.flags, u.st_lo, u.st_up, al, au);
+    u.act_lo = al[0];
+    u.act_up = au[0];
+}
+template <typename R, bool UNI>
+SRE_DEV void qcp_consts(const KCfg<R> &cfg, const QcpUni<R> &uni, const R *params, long long n,
+                        typename Env<SRE_QCP, R>::Consts &c, R *st_lo, R *st_up, R *act_lo, R *act_up) {
+    if constexpr (UNI) {
+        c = uni.c;
+#pragma unroll
+        for (int i = 0; i < 4; i++) { st_lo[i] = uni.st_lo[i]; st_up[i] = uni.st_up[i]; }
+        act_lo[0] = uni.act_lo;
+        act_up[0] = uni.act_up;
+    } else {
+        qcp_load_consts<R>(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
+    }
+}
+
 // forward over the horizon; writes the tape (states, carries) the adjoint reads
-template <typename R>
+template <typename R, bool UNI = false>
 __global__ void __launch_bounds__(128)
-qcp_diff_forward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, const R *s0, const R *thdd0,
+qcp_diff_forward_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ QcpUni<R> uni, const R *params, const R *s0, const R *thdd0,
                         const R *act, long long N, long long H, R *states, R *thdd, R *rew, unsigned char *done) {
     using D = QcpDiff<R>;
     const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     typename D::Cn c;
     R st_lo[4], st_up[4], act_lo[1], act_up[1];
-    qcp_load_consts<R>(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
+    qcp_consts<R, UNI>(cfg, uni, params, n, c, st_lo, st_up, act_lo, act_up);
     R s[4];
     row4_load(s0 + n * 4, s);
     R carry = thdd0 ? thdd0[n] : (R)0;
@@ -212,9 +243,9 @@ qcp_diff_forward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, co
 }
 
 // adjoint through the horizon: one thread walks its environment's tape backwards, recomputing the RK4 stages
-template <typename R>
+template <typename R, bool UNI = false>
 __global__ void __launch_bounds__(128)
-qcp_diff_backward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, const R *states, const R *thdd,
+qcp_diff_backward_kernel(const __grid_constant__ KCfg<R> cfg, const __grid_constant__ QcpUni<R> uni, const R *params, const R *states, const R *thdd,
                          const R *act, const R *g_states, const R *g_rew, const R *g_thdd, long long N, long long H,
                          R *g_s0, R *g_act, R *g_thdd0) {
     using D = QcpDiff<R>;
@@ -222,7 +253,7 @@ qcp_diff_backward_kernel(const __grid_constant__ KCfg<R> cfg, const R *params, c
     if (n >= N) return;
     typename D::Cn c;
     R st_lo[4], st_up[4], act_lo[1], act_up[1];
-    qcp_load_consts<R>(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
+    qcp_consts<R, UNI>(cfg, uni, params, n, c, st_lo, st_up, act_lo, act_up);
     R lam[4], lam_c;
 #pragma unroll
     for (int i = 0; i < 4; i++) lam[i] = g_states ? g_states[(H * N + n) * 4 + i] : (R)0;
@@ -403,16 +434,29 @@ SRE_DEV void qcp_load_consts2(const KCfg<float> &cfg, const float *params, long 
 #ifndef SRE_D2F_MINB
 #define SRE_D2F_MINB 1
 #endif
+struct QcpUni2 {  // QcpUni for the packed kernel: the constants as {value, value} pairs, packed on the host
+    QcpDiff2::Cn c;
+    float st_lo[4], st_up[4], act_lo, act_up;
+};
+template <bool UNI>
 __global__ void __launch_bounds__(128, SRE_D2F_MINB)
-qcp_diff_forward2_kernel(const __grid_constant__ KCfg<float> cfg, const float *params, const float *s0, const float *thdd0,
-                         const float *act, long long N, long long H, float *states, float *thdd, float *rew,
-                         unsigned char *done) {
+qcp_diff_forward2_kernel(const __grid_constant__ KCfg<float> cfg, const __grid_constant__ QcpUni2 uni, const float *params,
+                         const float *s0, const float *thdd0, const float *act, long long N, long long H, float *states,
+                         float *thdd, float *rew, unsigned char *done) {
     using D = QcpDiff2;
     const long long n = 2 * ((long long)blockIdx.x * blockDim.x + threadIdx.x);
     if (n >= N) return;
     D::Cn c;
     float st_lo[8], st_up[8], act_lo[2], act_up[2];
-    qcp_load_consts2(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
+    if constexpr (UNI) {
+        c = uni.c;
+#pragma unroll
+        for (int i = 0; i < 4; i++) { st_lo[i] = st_lo[4 + i] = uni.st_lo[i]; st_up[i] = st_up[4 + i] = uni.st_up[i]; }
+        act_lo[0] = act_lo[1] = uni.act_lo;
+        act_up[0] = act_up[1] = uni.act_up;
+    } else {
+        qcp_load_consts2(cfg, params, n, c, st_lo, st_up, act_lo, act_up);
+    }
     const bool simple = cfg.flags & SRE_F_SIMPLE_DYN;
     P2 s[4];
     {
@@ -539,16 +583,44 @@ static int launch_diff_forward(const sre_env_cfg *cfg, const void *params, const
         if (n % 2 == 0 && !diff_scalar_forced() && al(s0, 16) && al(states, 16) && al(thdd0, 8) && al(act, 8) &&
             al(thdd, 8) && al(rew, 8) && al(done, 2)) {
             const unsigned blocks = (unsigned)((n / 2 + 127) / 128);
-            qcp_diff_forward2_kernel<<<blocks, 128, 0, s>>>(k, (const float *)params, (const float *)s0,
-                                                            (const float *)thdd0, (const float *)act, n, horizon,
-                                                            (float *)states, (float *)thdd, (float *)rew, done);
+            QcpUni2 u2;
+            memset(&u2, 0, sizeof u2);
+            if (!params) {
+                QcpUni<float> u;
+                qcp_make_uni<float>(k, u);
+                auto hp = [](float a) { P2 p; unsigned int b; memcpy(&b, &a, 4); p.v = ((unsigned long long)b << 32) | b; return p; };
+                const auto &a = u.c;
+                u2.c.M00 = hp(a.M00); u2.c.M11 = hp(a.M11); u2.c.nM00M11 = hp(-(a.M00 * a.M11)); u2.c.mpl = hp(a.mpl);
+                u2.c.nmpl = hp(-a.mpl); u2.c.k_u = hp(a.k_u); u2.c.nk_xd = hp(-a.k_xd); u2.c.nB_eq = hp(-a.B_eq);
+                u2.c.nB_p = hp(-a.B_p); u2.c.nmplg = hp(-a.mplg); u2.c.mtg = hp(a.mtg); u2.c.nmpl2 = hp(-a.mpl2);
+                u2.c.mu_c = hp(a.mu_c);
+                u2.c.tn0 = u2.c.tn1 = a.thold_neg; u2.c.tp0 = u2.c.tp1 = a.thold_pos;
+                for (int i = 0; i < 4; i++) { u2.st_lo[i] = u.st_lo[i]; u2.st_up[i] = u.st_up[i]; }
+                u2.act_lo = u.act_lo; u2.act_up = u.act_up;
+                qcp_diff_forward2_kernel<true><<<blocks, 128, 0, s>>>(k, u2, nullptr, (const float *)s0, (const float *)thdd0,
+                                                                      (const float *)act, n, horizon, (float *)states,
+                                                                      (float *)thdd, (float *)rew, done);
+            } else {
+                qcp_diff_forward2_kernel<false><<<blocks, 128, 0, s>>>(k, u2, (const float *)params, (const float *)s0,
+                                                                       (const float *)thdd0, (const float *)act, n, horizon,
+                                                                       (float *)states, (float *)thdd, (float *)rew, done);
+            }
             SRE_CUDA(cudaGetLastError());
             return 0;
         }
     }
     const unsigned blocks = (unsigned)((n + 127) / 128);
-    qcp_diff_forward_kernel<R><<<blocks, 128, 0, s>>>(k, (const R *)params, (const R *)s0, (const R *)thdd0,
-                                                      (const R *)act, n, horizon, (R *)states, (R *)thdd, (R *)rew, done);
+    QcpUni<R> u;
+    memset(&u, 0, sizeof u);
+    if (!params) {
+        qcp_make_uni<R>(k, u);
+        qcp_diff_forward_kernel<R, true><<<blocks, 128, 0, s>>>(k, u, nullptr, (const R *)s0, (const R *)thdd0, (const R *)act, n,
+                                                                horizon, (R *)states, (R *)thdd, (R *)rew, done);
+    } else {
+        qcp_diff_forward_kernel<R, false><<<blocks, 128, 0, s>>>(k, u, (const R *)params, (const R *)s0, (const R *)thdd0,
+                                                                 (const R *)act, n, horizon, (R *)states, (R *)thdd, (R *)rew,
+                                                                 done);
+    }
     SRE_CUDA(cudaGetLastError());
     return 0;
 }
@@ -561,10 +633,19 @@ static int launch_diff_backward(const sre_env_cfg *cfg, const void *params, cons
     make_kcfg<R>(*cfg, k);
     // (a packed two-environment adjoint was measured: 166-190 registers, 2.5e10 steps/s against 3.6e10 of this kernel)
     const unsigned blocks = (unsigned)((n + 127) / 128);
-    qcp_diff_backward_kernel<R><<<blocks, 128, 0, s>>>(k, (const R *)params, (const R *)states, (const R *)thdd,
-                                                       (const R *)act, (const R *)g_states, (const R *)g_rew,
-                                                       (const R *)g_thdd, n, horizon, (R *)g_s0, (R *)g_act,
-                                                       (R *)g_thdd0);
+    QcpUni<R> u;
+    memset(&u, 0, sizeof u);
+    if (!params) {
+        qcp_make_uni<R>(k, u);
+        qcp_diff_backward_kernel<R, true><<<blocks, 128, 0, s>>>(k, u, nullptr, (const R *)states, (const R *)thdd, (const R *)act,
+                                                                 (const R *)g_states, (const R *)g_rew, (const R *)g_thdd, n,
+                                                                 horizon, (R *)g_s0, (R *)g_act, (R *)g_thdd0);
+    } else {
+        qcp_diff_backward_kernel<R, false><<<blocks, 128, 0, s>>>(k, u, (const R *)params, (const R *)states, (const R *)thdd,
+                                                                  (const R *)act, (const R *)g_states, (const R *)g_rew,
+                                                                  (const R *)g_thdd, n, horizon, (R *)g_s0, (R *)g_act,
+                                                                  (R *)g_thdd0);
+    }
     SRE_CUDA(cudaGetLastError());
     return 0;
 }

@@ -251,3 +251,27 @@ def test_packed_pair_kernels_agree_with_the_scalar_kernels(E, simple, monkeypatc
         scale = max(np.abs(b).max(), 1.0)
         err = np.abs(a.astype(np.float64) - b).max() / scale
         assert err < tol, (name, err)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-12), (torch.float32, 1e-5)])
+def test_launch_argument_constants_agree_with_per_env_parameters(E, dtype, tol):
+    """Without a parameter tensor the derived cart-pole constants are computed once on the host and passed as launch
+    arguments (constant-bank operands, qcp_diff_*_kernel<.., UNI = true>); with a [N, dp] tensor holding the same nominal
+    values every lane derives them itself.  Same formulas: forward tape and gradients agree to round-off."""
+    from simurlacra_b200 import _lib as L
+
+    H, N = 30, 512
+    cfg = _cfg(E, False, dtype)
+    g = torch.Generator().manual_seed(9)
+    s0 = ((torch.rand(N, 4, generator=g, dtype=torch.float64) - 0.5) * torch.tensor([0.4, 6.0, 1.0, 4.0], dtype=torch.float64)).to(dtype).to(DEV)
+    act = ((torch.rand(H, N, generator=g, dtype=torch.float64) - 0.5) * 14.0).to(dtype).to(DEV)
+    g_rew = torch.ones(H, N, dtype=dtype, device=DEV)
+    params = torch.tensor(E.nominal_params(L.QCP, long_pole=True), dtype=dtype, device=DEV).repeat(N, 1).contiguous()
+    out = []
+    for p in (None, params):
+        states, thdd, rew, done = E.qcp_diff_forward(cfg, p, s0, act)
+        g_s0, g_act, _ = E.qcp_diff_backward(cfg, p, states, thdd, act, g_rew=g_rew)
+        out.append((states, rew, g_s0, g_act))
+    for a, b in zip(*out):
+        scale = max(1.0, float(b.abs().max()))
+        assert float((a - b).abs().max()) < tol * scale * 50
